@@ -1,0 +1,867 @@
+/*
+ * photon_oracle.cpp -- TEST INFRASTRUCTURE, NOT PRODUCT.
+ *
+ * A CPU restatement of photon's ray-tracing hot path
+ *   cuda_codes/parallel_ray_tracing.cu:3078-3775  (start_ray_tracing, host driver)
+ *   cuda_codes/parallel_ray_tracing.cu:1923-2243  (parallel_ray_tracing, per-ray kernel)
+ *   cuda_codes/trace_rays_through_density_gradients.h (volume integration + field ingest)
+ * written function by function after the reference, keeping its operand types and
+ * evaluation order (including the float/double promotions that unsuffixed literals
+ * cause) so that it can serve as the parity checker for the CUDA library.  Each
+ * function cites the reference lines it restates.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load this.  The product library never links or calls it.
+ *
+ * Parity pin: the reference ships no golden vectors for this path;
+ * this restatement is pinned against the reference's own source compiled for the
+ * host (oracle/build_ref.sh -> oracle/_ref/libphoton_ref_cpu.so) on recorded inputs,
+ * see tests/test_oracle_vs_reference.py and tests/golden/.
+ *
+ * Deliberate differences from the reference (all documented in DESIGN.md):
+ *  - the image is accumulated in double and rounded to float once (the reference uses
+ *    float atomicAdd in a non-deterministic order; any order lies within 1e-6 of this);
+ *  - bilinear splat: an image index < 0 (reference defect, prt.cu:2223-2228) is dropped
+ *    instead of written out of bounds;
+ *  - intermediate-position dumps are bounds-checked against num_lightrays_save;
+ *  - NRRD load failure returns (image untouched) instead of exit();
+ *  - cuRAND noise (add_pos_noise / add_ngrad_noise; time-seeded in the reference) is
+ *    replaced by a counter-based normal generator: statistical parity only.
+ *
+ * Build: make -C oracle      (g++ -O2 -fopenmp -ffp-contract=off)
+ */
+#include <cfloat>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#include "../include/photon_abi.h"
+#include "nrrd_read.h"
+
+namespace {
+
+// ---------------------------------------------------------------------------
+// float3 arithmetic with the operation order of the reference's operator layer
+// (CubicInterpolationCUDA/code/internal/cutil_math_bugfixes.h:302-409,
+//  float3_operators.h:48-86).
+// ---------------------------------------------------------------------------
+struct v3 { float x, y, z; };
+struct v4 { float x, y, z, w; };
+inline v3 mk(float x, float y, float z) { return v3{x, y, z}; }
+inline v3 operator+(v3 a, v3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline v3 operator-(v3 a, v3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline v3 operator-(v3 a) { return mk(-a.x, -a.y, -a.z); }
+inline v3 operator*(v3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+inline v3 operator*(float s, v3 a) { return mk(a.x * s, a.y * s, a.z * s); }
+inline v3 operator/(v3 a, float s) { float inv = 1.0f / s; return a * inv; }   // :352-356
+inline float dot(v3 a, v3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }      // :392-395
+inline v3 normalize(v3 v) { float inv = 1.0f / sqrtf(dot(v, v)); return v * inv; }  // :405-409
+inline v3 nan3() { float n = std::nanf(""); return mk(n, n, n); }
+inline bool any_nan(v3 a) { return std::isnan(a.x) || std::isnan(a.y) || std::isnan(a.z); }
+
+struct Ray {           // light_ray_data_t, prt.h:102-112
+    v3 pos, dir;
+    float wavelength;
+    double radiance;
+};
+inline void kill(Ray &r) {
+    r.pos = nan3(); r.dir = nan3(); r.wavelength = std::nanf(""); r.radiance = std::nan("");
+}
+
+struct SourcePoint { float x, y, z; double radiance; int diameter_index; };
+
+// ---------------------------------------------------------------------------
+// Counter-based RNG used for the optional modes (Philox4x32-10, Salmon et al. SC'11,
+// as published in Random123 / cuRAND's curand_philox4x32_x.h).  The reference itself
+// never uses Philox; the product offers it as PHOTON_RNG=philox and this is its checker.
+// ---------------------------------------------------------------------------
+inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+    for (int r = 0; r < 10; r++) {
+        uint64_t p0 = (uint64_t)M0 * c[0], p1 = (uint64_t)M1 * c[2];
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0;
+        uint32_t n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+        uint32_t n3 = (uint32_t)p0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+        k0 += W0; k1 += W1;
+    }
+}
+// uniform in [0,1): top 24 bits
+inline float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+// ---------------------------------------------------------------------------
+// (a3) Ray generation -- prt.cu:71-237
+// ---------------------------------------------------------------------------
+Ray generate_ray(float lens_pitch, float image_distance, const scattering_data_t &sc, int mie,
+                 const SourcePoint &sp, int rpp, float wavelength, float f_number,
+                 float r1, float r2, float cone_ratio) {
+    float xc = sp.x, yc = sp.y, zc = sp.z;
+    float x_lens, y_lens;
+    if (rpp == 1) { x_lens = 0.0f; y_lens = 0.0f; }                     // :111-116 chief ray
+    else {
+        // :123-124  float*double literal -> whole product in double, narrowed on store
+        x_lens = (float)((double)cone_ratio * 1.0 * (double)lens_pitch * (double)r1 * cos(2 * M_PI * (double)r2));
+        y_lens = (float)((double)cone_ratio * 1.0 * (double)lens_pitch * (double)r1 * sin(2 * M_PI * (double)r2));
+    }
+    float theta = atanf(-(x_lens - xc) / (image_distance - zc));        // :128
+    float phi = atanf(-(y_lens - yc) / (image_distance - zc));          // :130
+
+    double irradiance;
+    if (mie) {
+        float dang = sc.scattering_angle[1] - sc.scattering_angle[0];   // :147
+        v3 beam = mk(sc.beam_propagation_vector[0], sc.beam_propagation_vector[1], sc.beam_propagation_vector[2]);
+        v3 d = normalize(mk(tanf(theta), tanf(phi), -1.0f));            // :162-165
+        float rot[3];
+        for (int i = 0; i < 3; i++) {                                   // :170-177
+            v3 row = mk(sc.inverse_rotation_matrix[i * 3 + 0], sc.inverse_rotation_matrix[i * 3 + 1],
+                        sc.inverse_rotation_matrix[i * 3 + 2]);
+            rot[i] = dot(row, d);
+        }
+        d = normalize(mk(rot[0], rot[1], rot[2]));                      // :178-180
+        // angleBetween (f3.h:77-86) returns degrees as float; caller converts back (:184)
+        float dp = beam.x * d.x + beam.y * d.y + beam.z * d.z;
+        float deg = (float)((double)acosf(dp) * 180.0 / M_PI);
+        float ang = (float)((double)deg * M_PI / 180.0);
+        float a = (ang - sc.scattering_angle[0]) / dang;                // :190
+        int al = (int)a, au = al + 1;                                   // :193-194
+        float il = sc.scattering_irradiance[al * sc.num_diameters + sp.diameter_index];   // :196
+        float iu = sc.scattering_irradiance[au * sc.num_diameters + sp.diameter_index];   // :198
+        float ir = il + (a - (float)al) / (float)(au - al) * (iu - il); // :201
+        irradiance = (double)ir * sp.radiance;                          // :204
+    } else {
+        irradiance = sp.radiance;                                       // :217
+    }
+    Ray r;
+    r.pos = mk(xc, yc, zc);
+    r.dir = normalize(mk(tanf(theta), tanf(phi), -1.0f));               // :228
+    r.wavelength = wavelength;
+    r.radiance = (double)(1 / (f_number * f_number)) * irradiance;      // :233 (1/float -> float)
+    return r;
+}
+
+// ---------------------------------------------------------------------------
+// (a10) Field ingest -- trace.h:1663-1817 loadNRRD, 1820-2002 setData, 2004-2105 readDatafromFile
+// ---------------------------------------------------------------------------
+struct Field {
+    v3 min_bound, max_bound, spacing;
+    int W = 0, H = 0, D = 0;
+    float step_size = 0, data_min = 0;
+    std::vector<v4> g;   // (dn/dx, dn/dy, dn/dz, n-1), x fastest
+};
+
+bool load_field(const char *path, Field &F, std::string &err) {
+    onrrd::Volume vol;
+    if (!onrrd::load(path, vol)) { err = vol.error; return false; }
+    int sx = vol.nx, sy = vol.ny, sz = vol.nz;
+    double xmin = vol.origin[0], dx = vol.spacing[0], xmax = xmin + (sx - 1) * dx;   // :1698-1700
+    double ymin = vol.origin[1], dy = vol.spacing[1], ymax = ymin + (sy - 1) * dy;   // :1701-1703
+    double zmin = vol.origin[2] - 750e3, dz = vol.spacing[2], zmax = zmin + (sz - 1) * dz;  // :1704-1706
+    // :1713-1716 with data_min=0, data_max=1024 (trace.h:2037-2038): depth is cut at 1024
+    int data_max = 1024;
+    if (data_max > sz) data_max = sz;
+    if (sz > data_max) sz = data_max;
+    size_t n = (size_t)sx * sy * sz;
+    std::vector<float> nm1(n);
+    const float K = 0.225e-3f;                                          // :1729 Gladstone-Dale
+    for (size_t i = 0; i < n; i++) nm1[i] = K * (vol.rho[i] * 1.0f);    // :1740-1748
+    F.min_bound = mk((float)xmin, (float)ymin, (float)zmin);            // :2065
+    F.max_bound = mk((float)xmax, (float)ymax, (float)zmax);            // :2066
+    F.W = sx; F.H = sy; F.D = sz;
+    F.spacing = mk((float)dx, (float)dy, (float)dz);                    // :2074-2076
+    F.g.resize(n);
+    F.data_min = FLT_MAX;
+    float gx = F.spacing.x, gy = F.spacing.y, gz = F.spacing.z;
+    size_t W = sx, H = sy, Dp = sz;
+    auto at = [&](size_t x, size_t y, size_t z) { return nm1[z * W * H + y * W + x]; };
+    // setData :1856-1995.  Literals such as 3.0/2 are double; result narrowed on store.
+    for (size_t z = 0; z < Dp; z++)
+        for (size_t y = 0; y < H; y++)
+            for (size_t x = 0; x < W; x++) {
+                size_t loc = z * W * H + y * W + x;
+                if (nm1[loc] < F.data_min) F.data_min = nm1[loc];
+                v4 o;
+                if (x < 1) o.x = (float)((-3.0 / 2 * at(x, y, z) + 2 * at(x + 1, y, z) - 1.0 / 2 * at(x + 2, y, z)) / gx);
+                else if (x >= W - 1) o.x = (float)((3.0 / 2 * at(x, y, z) - 2 * at(x - 1, y, z) + 1.0 / 2 * at(x - 2, y, z)) / gx);
+                else o.x = (at(x + 1, y, z) - at(x - 1, y, z)) / (2 * gx);
+                if (y < 1) o.y = (float)((-3.0 / 2 * at(x, y, z) + 2 * at(x, y + 1, z) - 1.0 / 2 * at(x, y + 2, z)) / gy);
+                else if (y >= H - 1) o.y = (float)((3.0 / 2 * at(x, y, z) - 2 * at(x, y - 1, z) + 1.0 / 2 * at(x, y - 2, z)) / gy);
+                else o.y = (float)((at(x, y + 1, z) - at(x, y - 1, z)) / (2.0 * gy));
+                if (z < 1) o.z = (float)((-3.0 / 2 * at(x, y, z) + 2 * at(x, y, z + 1) - 1.0 / 2 * at(x, y, z + 2)) / gz);
+                else if (z >= Dp - 1) o.z = (float)((3.0 / 2 * at(x, y, z) - 2 * at(x, y, z - 1) + 1.0 / 2 * at(x, y, z - 2)) / gz);
+                else o.z = (at(x, y, z + 1) - at(x, y, z - 1)) / (2 * gz);
+                o.w = nm1[loc];
+                F.g[loc] = o;
+            }
+    // :2086-2098 step = min spacing (fmin of doubles, then float)
+    float step = (float)fmin(dx, dy);
+    step = step < dz ? step : (float)dz;
+    F.step_size = step;
+    return true;
+}
+
+// ---------------------------------------------------------------------------
+// Software tex3D: unnormalised coordinates, texel centres at +0.5, clamp addressing,
+// linear filter (Host_Init, trace.h:1620-1642; CUDA Programming Guide "Linear Filtering":
+// xB = x-0.5, i = floor(xB), alpha = frac(xB) kept in 1.8 fixed point).
+// weight_bits = 0 -> exact float fractions; 8 -> hardware-like 8 fractional bits.
+// ---------------------------------------------------------------------------
+struct Sampler { const Field *F; int weight_bits; };
+
+inline float quant(float a, int bits) {
+    if (bits <= 0) return a;
+    float s = (float)(1 << bits);
+    return floorf(a * s + 0.5f) / s;
+}
+inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+v4 tex3d(const Sampler &S, float x, float y, float z) {
+    const Field &F = *S.F;
+    float xb = x - 0.5f, yb = y - 0.5f, zb = z - 0.5f;
+    float fx = floorf(xb), fy = floorf(yb), fz = floorf(zb);
+    float a = quant(xb - fx, S.weight_bits), b = quant(yb - fy, S.weight_bits), c = quant(zb - fz, S.weight_bits);
+    int i = (int)fx, j = (int)fy, k = (int)fz;
+    int i0 = clampi(i, 0, F.W - 1), i1 = clampi(i + 1, 0, F.W - 1);
+    int j0 = clampi(j, 0, F.H - 1), j1 = clampi(j + 1, 0, F.H - 1);
+    int k0 = clampi(k, 0, F.D - 1), k1 = clampi(k + 1, 0, F.D - 1);
+    size_t W = F.W, WH = (size_t)F.W * F.H;
+    const v4 &c000 = F.g[k0 * WH + j0 * W + i0], &c100 = F.g[k0 * WH + j0 * W + i1];
+    const v4 &c010 = F.g[k0 * WH + j1 * W + i0], &c110 = F.g[k0 * WH + j1 * W + i1];
+    const v4 &c001 = F.g[k1 * WH + j0 * W + i0], &c101 = F.g[k1 * WH + j0 * W + i1];
+    const v4 &c011 = F.g[k1 * WH + j1 * W + i0], &c111 = F.g[k1 * WH + j1 * W + i1];
+    float w000 = (1 - a) * (1 - b) * (1 - c), w100 = a * (1 - b) * (1 - c);
+    float w010 = (1 - a) * b * (1 - c), w110 = a * b * (1 - c);
+    float w001 = (1 - a) * (1 - b) * c, w101 = a * (1 - b) * c;
+    float w011 = (1 - a) * b * c, w111 = a * b * c;
+    v4 o;
+    o.x = w000 * c000.x + w100 * c100.x + w010 * c010.x + w110 * c110.x + w001 * c001.x + w101 * c101.x + w011 * c011.x + w111 * c111.x;
+    o.y = w000 * c000.y + w100 * c100.y + w010 * c010.y + w110 * c110.y + w001 * c001.y + w101 * c101.y + w011 * c011.y + w111 * c111.y;
+    o.z = w000 * c000.z + w100 * c100.z + w010 * c010.z + w110 * c110.z + w001 * c001.z + w101 * c101.z + w011 * c011.z + w111 * c111.z;
+    o.w = w000 * c000.w + w100 * c100.w + w010 * c010.w + w110 * c110.w + w001 * c001.w + w101 * c101.w + w011 * c011.w + w111 * c111.w;
+    return o;
+}
+
+// ---------------------------------------------------------------------------
+// (a4) Box entry -- trace.h:100-186 IntersectWithVolume
+// ---------------------------------------------------------------------------
+bool enter_volume(v3 &pos, v3 dir, v3 p1, v3 p2) {
+    float tnear = -(FLT_MAX - 1);
+    float tfar = FLT_MAX;
+    float t1 = (p1.x - pos.x) / dir.x, t2 = (p2.x - pos.x) / dir.x;
+    if (t1 > t2) { float t = t1; t1 = t2; t2 = t; }
+    if (t1 > tnear) tnear = t1;
+    if (t2 < tfar) tfar = t2;
+    if (tnear > tfar) return false;
+    if (tfar < 0.0) return false;
+    t1 = (p1.y - pos.y) / dir.y; t2 = (p2.y - pos.y) / dir.y;
+    if (t1 > t2) { float t = t1; t1 = t2; t2 = t; }
+    if (t1 > tnear) tnear = t1;
+    if (t2 < tfar) tfar = t2;
+    if (tnear > tfar) return false;
+    if (tfar < 0.0) return false;
+    t1 = (p1.z - pos.z) / dir.z; t2 = (p2.z - pos.z) / dir.z;
+    if (t1 > t2) { float t = t1; t1 = t2; t2 = t; }
+    float t;
+    if (t1 >= 0 && t1 > tnear) tnear = t1;                              // :168 (z slab differs)
+    if (t2 < tfar) tfar = t2;
+    if (tnear > tfar) return false;
+    if (tfar < 0.0) return false;
+    else if (tnear < 0) t = tfar;                                       // :176-177
+    else t = tnear;
+    pos.x += dir.x * t; pos.y += dir.y * t; pos.z += dir.z * t;
+    return true;
+}
+
+// (a5) trace.h:195-215
+inline v3 lookup_index(v3 pos, const Field &F, v3 scale) {
+    v3 off = pos - F.min_bound;
+    v3 fn = mk(scale.x * off.x, scale.y * off.y, scale.z * off.z);
+    return mk(1 + fn.x * (float)(F.W - 2), 1 + fn.y * (float)(F.H - 2), 1 + fn.z * (float)(F.D - 2));
+}
+// (a6) trace.h:217-251
+inline bool lookup_ok(v3 l, const Field &F) {
+    return !(l.x < 0 || l.y < 0 || l.z < 0 || l.x >= F.W || l.y >= F.H || l.z >= F.D);
+}
+inline bool inside_box(v3 p, const Field &F, v3 l) {
+    if (p.x < F.min_bound.x || p.y < F.min_bound.y || p.z < F.min_bound.z ||
+        p.x >= F.max_bound.x || p.y >= F.max_bound.y || p.z >= F.max_bound.z) return false;
+    return lookup_ok(l, F);
+}
+
+struct NoiseGen {       // stand-in for curand_normal2(&states[ray]) -- statistical parity only
+    uint64_t ray; uint32_t ctr; uint32_t seed;
+    void normal2(float &a, float &b) {
+        uint32_t c[4] = {(uint32_t)ray, (uint32_t)(ray >> 32), ctr++, 0x6e6f6973u};
+        philox4x32_10(c, seed, 0x70686f74u);
+        float u = ((float)(c[0] >> 8) + 0.5f) * (1.0f / 16777216.0f);
+        float v = ((float)(c[1] >> 8) + 0.5f) * (1.0f / 16777216.0f);
+        float r = sqrtf(-2.0f * logf(u));
+        a = r * cosf(6.2831853f * v); b = r * sinf(6.2831853f * v);
+    }
+};
+
+struct Interm { v3 *pos, *dir; int n; bool on; };   // intermediate dump slots of one ray
+struct StepCount { long long steps; };
+
+// sample with the reference's "value below data_min" fallback (trace.h:1052-1065 etc.)
+inline v4 sample_with_fallback(const Sampler &S, v3 l, float data_min, const v4 &prev, float n_fallback_m1) {
+    v4 val = tex3d(S, l.x, l.y, l.z);
+    if (val.w < data_min) {
+        if (prev.w == 0) {
+            v4 t = tex3d(S, l.x, l.y, l.z - 1);
+            val = v4{t.x, t.y, t.z, n_fallback_m1};
+        } else val = prev;
+    }
+    return val;
+}
+
+// (a8) Euler, linear branch -- trace.h:770-894
+void euler(Ray &ray, const Field &F, const Sampler &S, v3 scale, bool ngrad_noise, float ngrad_std,
+           NoiseGen &ng, Interm im, StepCount &sc) {
+    float refractive_index = 1.000277f;
+    v4 prev{0, 0, 0, 0};
+    int loop = 0; const int loop_max = (int)1e7;
+    while (true) {
+        if (loop > loop_max) break;
+        v3 pos = ray.pos, dir = ray.dir;
+        if (im.on && loop < im.n) { im.pos[loop] = pos; im.dir[loop] = dir; }
+        v3 l = lookup_index(pos, F, scale);
+        if (!inside_box(pos, F, l) && loop != 0) break;
+        if (!lookup_ok(l, F)) {                                          // :806-813
+            pos = pos + F.step_size / (1 + F.data_min) * dir;
+            ray.pos = pos;
+            continue;
+        }
+        v4 val = sample_with_fallback(S, l, F.data_min, prev, refractive_index - 1);
+        float n_cur = 1 + val.w;
+        if (ngrad_noise) { float a, b; ng.normal2(a, b); val.x += a * ngrad_std; val.y += b * ngrad_std; }
+        v3 normal = mk(val.x, val.y, val.z);
+        dir = dir + F.step_size * normal;                                // :869 (not renormalised)
+        refractive_index = 1 + val.w;
+        pos = pos + F.step_size / n_cur * dir;                           // :875
+        ray.pos = pos; ray.dir = dir;
+        prev = val;
+        loop += 1; sc.steps++;
+    }
+}
+
+// (a7) RK4 (Sharma et al. 1982), linear branch -- trace.h:992-1181
+void rk4(Ray &ray, const Field &F, const Sampler &S, v3 scale, Interm im, StepCount &sc) {
+    const float refractive_index = 1.000277f;
+    v4 prev{0, 0, 0, 0};
+    int loop = 0; const int loop_max = (int)1e7;
+    while (true) {
+        if (loop > loop_max) break;
+        if (im.on && loop < im.n) { im.pos[loop] = ray.pos; im.dir[loop] = ray.dir; }
+        v3 pos = ray.pos;
+        v3 l = lookup_index(pos, F, scale);
+        if (!inside_box(pos, F, l) && loop != 0) break;                  // :1021
+        if (!lookup_ok(l, F)) {                                          // :1031-1038
+            pos = pos + F.step_size / (1 + F.data_min) * ray.dir;
+            ray.pos = pos;
+            continue;
+        }
+        v4 val = sample_with_fallback(S, l, F.data_min, prev, refractive_index - 1);
+        loop += 1;
+        val.w += 1;
+        float n_cur = val.w;                                             // :1071
+        v3 R = pos;
+        float dt = F.step_size / val.w;
+        v3 T = val.w * ray.dir;
+        v3 Dv = mk(val.w * val.x, val.w * val.y, val.w * val.z);
+        v3 A = dt * Dv;
+        // :1088  delta_t/2.0 and 1/8.0*delta_t are double expressions narrowed to float
+        pos = R + (float)((double)dt / 2.0) * T + (float)(1 / 8.0 * (double)dt) * A;
+        l = lookup_index(pos, F, scale);
+        if (!inside_box(pos, F, l)) break;                               // :1094 (step discarded)
+        prev = val; prev.w -= 1;
+        val = sample_with_fallback(S, l, F.data_min, prev, refractive_index - 1);
+        val.w += 1;
+        Dv = mk(val.w * val.x, val.w * val.y, val.w * val.z);
+        v3 B = dt * Dv;
+        pos = R + dt * T + (float)(1 / 2.0 * (double)dt) * B;            // :1131
+        l = lookup_index(pos, F, scale);
+        if (!inside_box(pos, F, l)) break;                               // :1135
+        prev = val; prev.w -= 1;
+        val = sample_with_fallback(S, l, F.data_min, prev, refractive_index - 1);
+        val.w += 1;
+        Dv = mk(val.w * val.x, val.w * val.y, val.w * val.z);
+        v3 C = dt * Dv;
+        const float sixth = (float)(1 / 6.0);
+        R = R + dt * (T + sixth * (A + 2.0f * B));                       // :1169
+        T = T + sixth * (A + 4.0f * B + C);                              // :1170
+        prev = val; prev.w -= 1;
+        ray.pos = R;
+        ray.dir = normalize(T / n_cur);                                  // :1178
+        sc.steps++;
+    }
+}
+
+// (a4) trace.h:1455-1544
+void trace_volume(Ray &ray, const Field &F, const Sampler &S, int algorithm, bool ngrad_noise,
+                  float ngrad_std, NoiseGen &ng, Interm im, StepCount &sc) {
+    v3 mn = F.min_bound, mx = F.max_bound;
+    v3 scale = mk(1.0f / (mx.x - mn.x), 1.0f / (mx.y - mn.y), 1.0f / (mx.z - mn.z));
+    v3 pos = ray.pos, dir = ray.dir;
+    if (pos.x <= mn.x || pos.y <= mn.y || pos.z <= mn.z || pos.x >= mx.x || pos.y >= mx.y || pos.z >= mx.z) {
+        if (!enter_volume(pos, dir, mn, mx)) return;                     // miss: ray unchanged
+    }
+    ray.pos = pos;
+    switch (algorithm) {
+        case 1: euler(ray, F, S, scale, ngrad_noise, ngrad_std, ng, im, sc); break;
+        case 2: rk4(ray, F, S, scale, im, sc); break;
+        default: break;   // 3 (rk45) and 4 (adams-bashforth): not restated yet -> pass-through
+    }
+}
+
+// ---------------------------------------------------------------------------
+// (a14) prt.cu:239-343, 345-380
+// ---------------------------------------------------------------------------
+v3 ray_sphere(v3 c, float R, v3 d, v3 p, char surface) {
+    float alpha = dot(d, d);
+    float beta = 2 * dot(d, p - c);
+    float gamma = dot(p - c, p - c) - R * R;
+    float disc = (float)((double)(beta * beta) - 4.0 * (double)alpha * (double)gamma);   // :276
+    if (disc < 0.0) return nan3();
+    float t1 = (float)((double)(-beta + sqrtf(disc)) / (2.0 * (double)alpha));          // :288
+    float t2 = (float)((double)(-beta - sqrtf(disc)) / (2.0 * (double)alpha));          // :289
+    float t;
+    if (surface == 'f') t = (R > 0) ? (t1 <= t2 ? t1 : t2) : (t1 >= t2 ? t1 : t2);
+    else t = (R > 0) ? (t1 <= t2 ? t1 : t2) : (t1 >= t2 ? t1 : t2);      // :318-336 (same choice)
+    return p + d * t;
+}
+float axis_distance(v3 p, v3 c, v4 plane) {
+    v3 n = mk(plane.x, plane.y, plane.z);
+    float tmin = dot(n, p - c) / (plane.x * plane.x + plane.y * plane.y + plane.z * plane.z);
+    v3 q = c + n * tmin;
+    return sqrtf(dot(p - q, p - q));
+}
+
+// (a13) prt.cu:383-1011
+void single_element(const element_data_t &el, v3 centre, v4 plane, Ray &ray) {
+    char type = el.element_type;
+    v3 dir = ray.dir, pos = ray.pos;
+    float wavelength = ray.wavelength;
+    double radiance = ray.radiance;
+    float a = plane.x, b = plane.y, c = plane.z, d = plane.w;
+    v3 n = mk(a, b, c);
+    float pitch = el.element_geometry.pitch;
+    double vertex = el.element_geometry.vertex_distance;
+    if (type == 't') {                                                   // :416-503
+        float f = el.element_properties.thin_lens_focal_length;
+        float t = -(dot(n, pos) + d) / dot(n, dir);
+        v3 hit = pos + dir * t;
+        float r = axis_distance(hit, centre, plane);
+        if ((double)r > (double)pitch / 2.0) { kill(ray); return; }
+        pos = hit;
+        dir = -(pos - centre) / f + dir;                                 // :494
+        dir = normalize(dir);
+    } else if (type == 'l') {                                            // :507-864
+        float Rf = el.element_geometry.front_surface_radius, Rb = el.element_geometry.back_surface_radius;
+        double nglass = el.element_properties.refractive_index;
+        float abbe = el.element_properties.abbe_number;
+        float transmission = el.element_properties.transmission_ratio;
+        float absorbance = el.element_properties.absorbance_rate;
+        float nmag = sqrtf(a * a + b * b + c * c);
+        float ds = (float)(+vertex / 2.0 - (double)Rf);                  // :551
+        v3 cf = centre + n * ds / nmag;                                  // :554
+        v3 hit = ray_sphere(cf, Rf, dir, pos, 'f');
+        float r = axis_distance(hit, centre, plane);
+        if ((double)r > (double)pitch / 2.0) { kill(ray); return; }      // :575 (NaN compares false)
+        v3 N = normalize(hit - cf);
+        float eta;
+        const float lD = 589.3f, lF = 486.1f, lC = 656.3f;
+        if (!std::isnan(abbe)) {                                         // :622-636
+            double disp = (1. / (double)(wavelength * wavelength) - (double)(1 / (lD * lD))) *
+                          ((nglass - 1) / (double)(abbe * (1 / (lF * lF) - 1 / (lC * lC))));
+            eta = (float)(1.0 / (nglass + disp));
+        } else eta = (float)(1.0 / nglass);                              // :641
+        float cosi = -dot(dir, N);
+        float rad = (float)(1.0 - (double)(eta * eta) * (1.0 - (double)(cosi * cosi)));   // :663
+        if (rad < 0.0) { kill(ray); return; }
+        dir = dir * eta + (eta * cosi - sqrtf(rad)) * N;                 // :687
+        dir = normalize(dir);
+        pos = hit;
+        ds = (float)(-vertex / 2 - (double)Rb);                          // :714
+        v3 cb = centre + n * ds / nmag;
+        hit = ray_sphere(cb, Rb, dir, pos, 'b');
+        r = axis_distance(hit, centre, plane);
+        if ((double)r > (double)pitch / 2.0) { kill(ray); return; }
+        N = normalize(-(hit - cb));                                      // :756-759
+        if (!std::isnan(abbe)) {                                         // :774-784
+            double disp = (1.0 / (double)(wavelength * wavelength) - 1.0 / (double)(lD * lD)) *
+                          ((nglass - 1) / (double)(abbe * (1 / (lF * lF) - 1 / (lC * lC))));
+            eta = (float)(nglass + disp);
+        } else eta = (float)nglass;
+        cosi = -dot(dir, N);
+        rad = (float)(1.0 - (double)(eta * eta) * (1.0 - (double)(cosi * cosi)));
+        if (rad < 0.0) { kill(ray); return; }
+        dir = eta * dir + (eta * cosi - sqrtf(rad)) * N;                 // :824
+        dir = normalize(dir);
+        if (absorbance != 0) {                                           // :838-853
+            float dist = sqrtf(dot(hit - pos, hit - pos));
+            radiance = (1.0 - (double)absorbance) * radiance * (double)dist;
+        } else radiance = (double)transmission * radiance;
+        pos = hit;
+    } else {                                                             // aperture :868-992
+        float nmag = sqrtf(a * a + b * b + c * c);
+        float ds = (float)(-vertex / 2.0);
+        float dt = d - ds * nmag;
+        float t = -(dot(n, pos) + dt) / dot(n, dir);
+        v3 hit = pos + dir * t;
+        float r = axis_distance(hit, centre, plane);
+        if ((double)r > (double)pitch / 2.0) { kill(ray); return; }
+        ds = (float)(+vertex / 2);
+        dt = d - ds * nmag;
+        t = -(dot(n, pos) + dt) / dot(n, dir);
+        hit = pos + dir * t;
+        r = axis_distance(hit, centre, plane);
+        if ((double)r > (double)pitch / 2.0) { kill(ray); return; }
+        pos = hit;
+    }
+    ray.dir = dir; ray.pos = pos; ray.wavelength = wavelength; ray.radiance = radiance;
+}
+
+// (a12) prt.cu:1274-1381.  Stages run from the highest system index down; a stage with
+// exactly one element is propagated through propagate_rays_through_single_element.
+// The reference hard-codes element 0 there (:1331-1333) and its multi-element branch
+// (prt.cu:1049-1272) is a no-op that also corrupts memory, so for num_elements > 1 its
+// behaviour is not a usable specification.  Default here: the
+// intended semantics (the element whose index matches the stage); literal_element0
+// reproduces the hard-coded index.  Identical for num_elements == 1 (all shipped scenes).
+void optical_system(const element_data_t *el, const v3 *centre, const v4 *plane, const int *sys_index,
+                    int ne, Ray &ray, bool literal_element0) {
+    int seq = 0;
+    for (int k = 0; k < ne; k++) if (seq <= sys_index[k]) seq = sys_index[k];
+    for (int stage = 0; stage < seq; stage++) {
+        int cnt = 0, which = 0;
+        for (int k = 0; k < ne; k++) if (seq - sys_index[k] == stage) { cnt++; which = k; }
+        if (cnt == 1) {
+            int e = literal_element0 ? 0 : which;
+            single_element(el[e], centre[e], plane[e], ray);
+            if (any_nan(ray.pos) || any_nan(ray.dir)) return;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Sensor -- prt.cu:1383-1543 (diffraction), 1545-1733 (apparent), 1735-1895 + 2189-2241 (bilinear)
+// ---------------------------------------------------------------------------
+struct Image { double *acc; int nx, ny; };
+
+inline bool sensor_hit(const Ray &ray, const camera_design_t &cam, bool pos_noise, float noise_std,
+                       NoiseGen &ng, v3 &hit) {
+    v3 nrm = mk(0.0f, 0.0f, 1.0f);
+    float d = -cam.z_sensor;
+    float t = -(dot(nrm, ray.pos) + d) / dot(nrm, ray.dir);
+    hit = ray.pos + ray.dir * t;
+    if (pos_noise) {
+        float a, b; ng.normal2(a, b);
+        hit.x += a * noise_std * cam.pixel_pitch;
+        hit.y += b * noise_std * cam.pixel_pitch;
+    }
+    return true;
+}
+inline double cos4(v3 d) {                                               // :1461-1463
+    float alpha = atanf(sqrtf((d.x / d.z) * (d.x / d.z) + (d.y / d.z) * (d.y / d.z)));
+    float c = cosf(alpha);
+    return (double)(c * c * c * c);
+}
+
+// shared erf-Gaussian splat of intersect_sensor_02 / create_apparent_image
+void erf_splat(Image &img, float d_x, float d_y, double radiance, double c4, float diam, float frac) {
+    const double pi = 3.141592653589793;
+    float X = (float)((double)d_x - 0.5), Y = (float)((double)d_y - 0.5);
+    float peak = (float)(radiance * c4 * 8.0 / pi);                      // :1474
+    float sqrt8 = sqrtf(8.0f);
+    int c0 = (int)floorf(X - frac * diam), c1 = (int)ceilf(X + frac * diam);
+    int r0 = (int)floorf(Y - frac * diam), r1 = (int)ceilf(Y + frac * diam);
+    for (int col = c0; col <= c1; col++)
+        for (int row = r0; row <= r1; row++) {
+            float rr = sqrtf(((float)col - X) * ((float)col - X) + ((float)row - Y) * ((float)row - Y));
+            bool ok = col >= 0 && col <= img.nx - 1 && row >= 0 && row <= img.ny - 1 && rr <= frac * diam;
+            if (!ok) continue;
+            // :1527-1531 -- (col - X - 0.5) is float-then-double; everything after is double
+            double ex = erf((double)sqrt8 * ((double)((float)col - X) - 0.5) / (double)diam) -
+                        erf((double)sqrt8 * ((double)((float)col - X) + 0.5) / (double)diam);
+            double ey = erf((double)sqrt8 * ((double)((float)row - Y) - 0.5) / (double)diam) -
+                        erf((double)sqrt8 * ((double)((float)row - Y) + 0.5) / (double)diam);
+            float inc = (float)((double)peak * pi / 32.0 * ex * ey);
+            img.acc[(size_t)row * img.nx + col] += (double)inc;
+        }
+}
+
+// (a16) returns final position (NaN if the ray misses the sensor)
+v3 sensor_diffraction(const Ray &ray, const camera_design_t &cam, bool pos_noise, float noise_std,
+                      NoiseGen &ng, Image &img) {
+    v3 hit; sensor_hit(ray, cam, pos_noise, noise_std, ng, hit);
+    float p1x = (float)((double)(-cam.pixel_pitch * (float)(cam.x_pixel_number - 1)) / 2.0);   // :1441
+    float p1y = (float)((double)(-cam.pixel_pitch * (float)(cam.y_pixel_number - 1)) / 2.0);
+    float d_x = (float)(cam.x_pixel_number - 1) - (hit.x - p1x) / cam.pixel_pitch;            // :1446 (x flipped)
+    float d_y = (hit.y - p1y) / cam.pixel_pitch;
+    if (d_x >= cam.x_pixel_number || d_y >= cam.y_pixel_number || d_x < 0 || d_y < 0) return nan3();
+    erf_splat(img, d_x, d_y, ray.radiance, cos4(ray.dir), cam.diffraction_diameter, 0.75f);
+    return hit;
+}
+
+// (a17) lens model 'n'
+v3 apparent_image(const Ray &ray_in, const camera_design_t &cam, bool pos_noise, float noise_std,
+                  NoiseGen &ng, Image &img, float z_object, float z_offset, const element_data_t &el) {
+    v3 dir = -ray_in.dir;                                                // :1553
+    v3 pos = ray_in.pos;
+    v3 nrm = mk(0.0f, 0.0f, -1.0f);
+    float d = z_object;
+    float t = -(dot(nrm, pos) + d) / dot(nrm, dir);
+    v3 hit = pos + dir * t;
+    float f = el.element_properties.thin_lens_focal_length;
+    float M = f / (z_object - z_offset - f);                             // :1589
+    hit.x = -hit.x * M; hit.y = -hit.y * M;
+    if (pos_noise) {
+        float a, b; ng.normal2(a, b);
+        hit.x += a * noise_std * cam.pixel_pitch; hit.y += b * noise_std * cam.pixel_pitch;
+    }
+    float p1x = (float)((double)(-cam.pixel_pitch * (float)(cam.x_pixel_number - 1)) / 2.0);
+    float p1y = (float)((double)(-cam.pixel_pitch * (float)(cam.y_pixel_number - 1)) / 2.0);
+    float d_x = (float)(cam.x_pixel_number - 1) - (hit.x - p1x) / cam.pixel_pitch;
+    float d_y = (hit.y - p1y) / cam.pixel_pitch;
+    if (d_x >= cam.x_pixel_number || d_y >= cam.y_pixel_number || d_x < 0 || d_y < 0) return nan3();
+    erf_splat(img, d_x, d_y, ray_in.radiance, cos4(dir), cam.diffraction_diameter, 1.00f);
+    return hit;
+}
+
+// (a15) bilinear 4-pixel splat
+v3 sensor_bilinear(const Ray &ray, const camera_design_t &cam, bool pos_noise, float noise_std,
+                   NoiseGen &ng, Image &img) {
+    v3 hit; sensor_hit(ray, cam, pos_noise, noise_std, ng, hit);
+    double c4 = cos4(ray.dir);
+    float p1x = (float)((double)(-cam.pixel_pitch * (float)(cam.x_pixel_number - 1)) / 2.0);
+    float p1y = (float)((double)(-cam.pixel_pitch * (float)(cam.y_pixel_number - 1)) / 2.0);
+    float d_x = (hit.x - p1x) / cam.pixel_pitch;                          // :1807 (no flip)
+    float d_y = (hit.y - p1y) / cam.pixel_pitch;
+    if (d_x >= cam.x_pixel_number || d_y >= cam.y_pixel_number || d_x < 0 || d_y < 0) return nan3();
+    float yl = (float)((double)d_y - 0.5), xl = (float)((double)d_x - 0.5);
+    double dii = (double)(ceilf(yl) - yl), djj = (double)(ceilf(xl) - xl);
+    double w[4] = {dii * djj, dii * (1 - djj), (1 - dii) * djj, (1 - dii) * (1 - djj)};
+    int ii0 = (int)(ceilf(yl) - 1), jj0 = (int)(ceilf(xl) - 1);
+    int ii[4] = {ii0, ii0, ii0 + 1, ii0 + 1};
+    int jj[4] = {jj0, jj0 + 1, jj0, jj0 + 1};
+    if (std::isnan(hit.x) || std::isnan(hit.y)) return hit;              // :2196
+    for (int k = 0; k < 4; k++) {                                        // :2219-2234
+        if (ii[k] < 0 || ii[k] >= cam.y_pixel_number || jj[k] < 0 || jj[k] >= cam.x_pixel_number) continue;
+        long idx = (long)(ii[k] - 1) * cam.x_pixel_number + jj[k] - 1;   // :2228
+        if (idx < 0) continue;                                           // reference writes out of bounds here
+        float inc = (float)(w[k] * ray.radiance * c4);
+        img.acc[idx] += (double)inc;
+    }
+    return hit;
+}
+
+}  // namespace
+
+// ===========================================================================
+// Host driver -- prt.cu:3078-3775
+// ===========================================================================
+extern "C" {
+
+/* extra outputs for the bench's cpu_baseline leg */
+static long long g_last_steps = 0, g_last_rays = 0;
+long long photon_oracle_last_ray_steps(void) { return g_last_steps; }
+long long photon_oracle_last_rays(void) { return g_last_rays; }
+
+/* Field ingest only: fills out[4*W*H*D] and meta = {min(3), max(3), spacing(3), step, data_min, W, H, D}. */
+int photon_oracle_load_field(const char *path, float *meta16, float *out, long long out_capacity_voxels) {
+    Field F; std::string err;
+    if (!load_field(path, F, err)) { fprintf(stderr, "photon_oracle: %s\n", err.c_str()); return 1; }
+    float m[16] = {F.min_bound.x, F.min_bound.y, F.min_bound.z, F.max_bound.x, F.max_bound.y, F.max_bound.z,
+                   F.spacing.x, F.spacing.y, F.spacing.z, F.step_size, F.data_min, (float)F.W, (float)F.H, (float)F.D, 0, 0};
+    memcpy(meta16, m, sizeof m);
+    if (out && out_capacity_voxels >= (long long)F.g.size()) memcpy(out, F.g.data(), F.g.size() * sizeof(v4));
+    return 0;
+}
+
+/* glibc lens-sample table of the reference: srand(10); interleaved rand() -- prt.cu:3228-3236 */
+void photon_oracle_lens_samples(int n, float *r1, float *r2) {
+    srand(10);
+    for (int k = 0; k < n; k++) {
+        r1[k] = (float)((double)rand() / (RAND_MAX));
+        r2[k] = (float)((double)rand() / (RAND_MAX));
+    }
+}
+
+void start_ray_tracing(float lens_pitch, float image_distance,
+                       scattering_data_t *scattering_data_p, char *scattering_type_str,
+                       lightfield_source_t *src_p, int rpp,
+                       float beam_wavelength, float f_number,
+                       int ne, double (*element_center)[3], element_data_t *element_data,
+                       double (*element_plane_parameters)[4], int *element_system_index,
+                       camera_design_t *cam_p, float *image_array,
+                       bool simulate_density_gradients, char *density_grad_filename,
+                       bool save_lightrays, char *pos_path, char *dir_path,
+                       int num_lightrays_save, int algorithm,
+                       bool add_pos_noise, float pos_noise_std,
+                       bool add_ngrad_noise, float ngrad_noise_std,
+                       float cone_ratio, bool save_intermediate, int num_intermediate) {
+    const scattering_data_t sc = *scattering_data_p;
+    const lightfield_source_t src = *src_p;
+    const camera_design_t cam = *cam_p;
+    const int mie = strcmp(scattering_type_str, "mie") == 0;
+    const int np = src.num_particles;
+    const int nx = cam.x_pixel_number, ny = cam.y_pixel_number;
+    const size_t npix = (size_t)nx * ny;
+
+    const char *wb = getenv("PHOTON_ORACLE_TEXW");        // "exact" (default) | "fixed8"
+    int weight_bits = (wb && strcmp(wb, "fixed8") == 0) ? 8 : 0;
+    const char *rng = getenv("PHOTON_RNG");               // "reference" (default) | "philox"
+    const bool philox = rng && strcmp(rng, "philox") == 0;
+    const bool literal_e0 = getenv("PHOTON_ORACLE_ELEMENT0") != nullptr;
+    uint32_t seed = 10;
+    if (const char *s = getenv("PHOTON_SEED")) seed = (uint32_t)strtoul(s, nullptr, 10);
+
+    // lens samples -- prt.cu:3216-3243
+    std::vector<float> r1(rpp > 0 ? rpp : 0), r2(rpp > 0 ? rpp : 0);
+    photon_oracle_lens_samples(rpp, r1.data(), r2.data());
+
+    std::vector<v3> centre(ne); std::vector<v4> plane(ne);
+    for (int k = 0; k < ne; k++) {                                       // :3250-3256 double -> float
+        centre[k] = mk((float)element_center[k][0], (float)element_center[k][1], (float)element_center[k][2]);
+        plane[k] = v4{(float)element_plane_parameters[k][0], (float)element_plane_parameters[k][1],
+                      (float)element_plane_parameters[k][2], (float)element_plane_parameters[k][3]};
+    }
+
+    Field F; Sampler S{&F, weight_bits};
+    if (simulate_density_gradients) {
+        std::string err;
+        if (!load_field(density_grad_filename, F, err)) {
+            fprintf(stderr, "photon_oracle: failed to load \"%s\": %s\n", density_grad_filename, err.c_str());
+            return;
+        }
+    }
+
+    int spn = src.source_point_number;
+    if (np < spn) spn = np;                                              // :3366-3368
+    if (spn <= 0 || rpp <= 0) return;
+    const long long rays_per_batch = (long long)spn * rpp;
+    int KMAX = np % spn == 0 ? np / spn : np / spn + 1;                  // :3506-3510
+
+    int nthreads = 1;
+#ifdef _OPENMP
+    nthreads = omp_get_max_threads();
+    if (const char *s = getenv("PHOTON_ORACLE_THREADS")) { int t = atoi(s); if (t > 0) nthreads = t; }
+#endif
+    std::vector<std::vector<double>> acc(nthreads);
+    for (auto &a : acc) a.assign(npix, 0.0);
+    long long total_steps = 0;
+
+    const bool dumps = save_lightrays && num_lightrays_save > 0;
+    std::vector<v3> fpos, fdir, ipos, idir;
+    if (dumps) { fpos.resize(num_lightrays_save); fdir.resize(num_lightrays_save); }
+    const bool interm = simulate_density_gradients && save_intermediate && num_intermediate > 0 && num_lightrays_save > 0;
+    if (interm) { ipos.resize((size_t)num_intermediate * num_lightrays_save); idir.resize(ipos.size()); }
+
+    for (int k = 0; k < KMAX; k++) {
+        const int n_min = k * spn;
+        if (dumps) { for (auto &v : fpos) v = nan3(); for (auto &v : fdir) v = nan3(); }
+        if (interm) { for (auto &v : ipos) v = nan3(); for (auto &v : idir) v = nan3(); }
+        long long batch_steps = 0;
+#pragma omp parallel for schedule(dynamic, 16) num_threads(nthreads) reduction(+ : batch_steps)
+        for (int lp = 0; lp < spn; lp++) {
+            int p = n_min + lp;
+            if (p >= np) continue;                                       // :1966-1968
+            int tid = 0;
+#ifdef _OPENMP
+            tid = omp_get_thread_num();
+#endif
+            Image img{acc[tid].data(), nx, ny};
+            SourcePoint sp{src.x[p], src.y[p], src.z[p], src.radiance[p], src.diameter_index[p]};
+            for (int lr = 0; lr < rpp; lr++) {
+                long long gid = (long long)lr + (long long)lp * rpp;     // batch-local ray id :1959
+                if (gid >= rays_per_batch) continue;
+                const bool save = dumps && gid < num_lightrays_save;
+                float u1 = r1[lr], u2 = r2[lr];                          // :2006 same draws for every point
+                if (philox) {
+                    uint64_t ray = (uint64_t)p * (uint64_t)rpp + (uint64_t)lr;   // global ray index
+                    uint32_t c[4] = {(uint32_t)ray, (uint32_t)(ray >> 32), 0u, 0u};
+                    philox4x32_10(c, seed, 0x50484f54u);
+                    u1 = u01(c[0]); u2 = u01(c[1]);
+                }
+                NoiseGen ng{(uint64_t)p * (uint64_t)rpp + (uint64_t)lr, 0u, seed};
+                Ray ray = generate_ray(lens_pitch, image_distance, sc, mie, sp, rpp, beam_wavelength,
+                                       f_number, u1, u2, cone_ratio);
+                if (simulate_density_gradients) {                        // :2033-2131
+                    v3 rp = ray.pos, rd = ray.dir;
+                    rp.z = (float)((double)rp.z - ((double)src.z_offset + 750e3));
+                    float pv[3], dv[3];
+                    for (int i = 0; i < 3; i++) {
+                        v3 row = mk(cam.inverse_rotation_matrix[i * 3], cam.inverse_rotation_matrix[i * 3 + 1],
+                                    cam.inverse_rotation_matrix[i * 3 + 2]);
+                        pv[i] = dot(row, rp); dv[i] = dot(row, rd);
+                    }
+                    ray.pos = mk(pv[0], pv[1], pv[2]); ray.dir = mk(dv[0], dv[1], dv[2]);
+                    Interm im{nullptr, nullptr, num_intermediate, false};
+                    if (interm && gid < num_lightrays_save) {
+                        im.pos = &ipos[(size_t)gid * num_intermediate]; im.dir = &idir[(size_t)gid * num_intermediate];
+                        im.on = true;
+                    }
+                    StepCount scnt{0};
+                    trace_volume(ray, F, S, algorithm, add_ngrad_noise, ngrad_noise_std, ng, im, scnt);
+                    batch_steps += scnt.steps;
+                    rp = ray.pos; rd = ray.dir;
+                    for (int i = 0; i < 3; i++) {
+                        v3 row = mk(cam.rotation_matrix[i * 3], cam.rotation_matrix[i * 3 + 1], cam.rotation_matrix[i * 3 + 2]);
+                        pv[i] = dot(row, rp); dv[i] = dot(row, rd);
+                    }
+                    rp = mk(pv[0], pv[1], pv[2]);
+                    rd = normalize(mk(dv[0], dv[1], dv[2]));
+                    ray.dir = rd;
+                    rp.z = (float)((double)rp.z + ((double)src.z_offset + 750e3));
+                    ray.pos = rp;
+                    if (any_nan(ray.dir) || any_nan(ray.pos)) continue;
+                }
+                if (save) fdir[gid] = ray.dir;                           // :2136-2141
+                if (element_data[0].element_type == 'n') {               // :2143-2158
+                    float z_obj = src.object_distance + src.z_offset;
+                    v3 fp = apparent_image(ray, cam, add_pos_noise, pos_noise_std, ng, img, z_obj, src.z_offset, element_data[0]);
+                    if (save) fpos[gid] = fp;
+                    continue;
+                }
+                optical_system(element_data, centre.data(), plane.data(), element_system_index, ne, ray, literal_e0);
+                if (any_nan(ray.dir) || any_nan(ray.pos)) continue;      // :2172-2176
+                v3 fp = cam.implement_diffraction
+                            ? sensor_diffraction(ray, cam, add_pos_noise, pos_noise_std, ng, img)
+                            : sensor_bilinear(ray, cam, add_pos_noise, pos_noise_std, ng, img);
+                if (cam.implement_diffraction) { if (save) fpos[gid] = fp; }
+                else if (!(std::isnan(fp.x) || std::isnan(fp.y))) { if (save) fpos[gid] = fp; }
+            }
+        }
+        total_steps += batch_steps;
+        if (dumps) {                                                     // :3561-3611
+            char name[32]; snprintf(name, sizeof name, "%04d.bin", k);
+            std::string fp = std::string(pos_path) + "/pos_" + name, fd = std::string(dir_path) + "/dir_" + name;
+            if (FILE *f = fopen(fp.c_str(), "wb")) { fwrite(fpos.data(), sizeof(v3), fpos.size(), f); fclose(f); }
+            if (FILE *f = fopen(fd.c_str(), "wb")) { fwrite(fdir.data(), sizeof(v3), fdir.size(), f); fclose(f); }
+        }
+        if (interm) {                                                    // :3613-3670
+            char name[32]; snprintf(name, sizeof name, "%04d.bin", k);
+            std::string fp = std::string(pos_path) + "/intermediate_pos_" + name;
+            std::string fd = std::string(dir_path) + "/intermediate_dir_" + name;
+            if (FILE *f = fopen(fp.c_str(), "wb")) { fwrite(ipos.data(), sizeof(v3), ipos.size(), f); fclose(f); }
+            if (FILE *f = fopen(fd.c_str(), "wb")) { fwrite(idir.data(), sizeof(v3), idir.size(), f); fclose(f); }
+        }
+    }
+    for (size_t i = 0; i < npix; i++) {
+        double s = 0;
+        for (int t = 0; t < nthreads; t++) s += acc[t][i];
+        image_array[i] = (float)((double)image_array[i] + s);
+    }
+    g_last_steps = total_steps;
+    g_last_rays = (long long)np * rpp;
+}
+
+}  // extern "C"
