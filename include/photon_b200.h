@@ -1,0 +1,106 @@
+/*
+ * photon_b200.h -- extended C ABI of libparallel_ray_tracing.so (B200 build).
+ *
+ * photon's Python binds exactly one symbol, start_ray_tracing (include/photon_abi.h).
+ * That call does everything per image: host->device copies, NRRD load + gradient
+ * precompute, the batch loop, device->host copy (cuda_codes/parallel_ray_tracing.cu:
+ * 3162-3309 uploads, 3323-3357 field, 3506-3559 launch loop, 3675 image copy-back).
+ * The entry points below expose the same stages separately so that a caller can keep
+ * a scene resident in HBM and re-trace it (what bench.py times as `value`), read
+ * counters, and shard source points over several GPUs / processes.  Plain pointers and
+ * sizes only; no C++ or torch types.
+ *
+ * Environment variables read by the library (the positional ABI cannot grow):
+ *   PHOTON_VERBOSE=1        progress lines like the reference's printf output
+ *   PHOTON_DEVICE=<n>       CUDA device ordinal (default: current device / 0)
+ *   PHOTON_RNG=reference    lens samples from srand(10)/rand(), the same rpp draws for
+ *                           every source point (prt.cu:3228-3236, 2006) [default]
+ *   PHOTON_RNG=philox       counter-based Philox4x32-10 keyed by the global ray index
+ *   PHOTON_SEED=<n>         seed for Philox lens samples and for the noise streams
+ *   PHOTON_SAMPLER=linear   software trilinear from a linear float4 buffer [default]
+ *   PHOTON_SAMPLER=texture  hardware tex3D<float4> (the reference's 9-bit filter weights)
+ *   PHOTON_SHARD=r/n        trace only the r-th of n contiguous source-point shards
+ *   PHOTON_GPUS=<n>         split the source points over n GPUs inside one call
+ */
+#ifndef PHOTON_B200_H_
+#define PHOTON_B200_H_
+
+#include "photon_abi.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct photon_scene photon_scene;   /* opaque: one scene resident on one GPU */
+
+/* Library / device queries. */
+int         photon_b200_abi_version(void);          /* bumps when this header changes */
+int         photon_b200_device_count(void);         /* 0 if no CUDA device is usable */
+const char *photon_b200_last_error(void);           /* "" if none; thread-local */
+
+/*
+ * Upload a scene: same arguments as start_ray_tracing minus the image and the dump
+ * paths (replaces prt.cu:3162-3357).  shard_index/shard_count select a contiguous range
+ * of source points (0/1 = all).  Returns NULL on failure (see photon_b200_last_error).
+ */
+photon_scene *photon_scene_create(float lens_pitch, float image_distance,
+                                  const scattering_data_t *scattering_data, const char *scattering_type_str,
+                                  const lightfield_source_t *lightfield_source, int lightray_number_per_particle,
+                                  float beam_wavelength, float aperture_f_number,
+                                  int num_elements, const double (*element_center)[3], const element_data_t *element_data,
+                                  const double (*element_plane_parameters)[4], const int *element_system_index,
+                                  const camera_design_t *camera_design,
+                                  bool simulate_density_gradients, const char *density_grad_filename,
+                                  int ray_tracing_algorithm,
+                                  bool add_pos_noise, float pos_noise_std,
+                                  bool add_ngrad_noise, float ngrad_noise_std,
+                                  float ray_cone_pitch_ratio,
+                                  int shard_index, int shard_count, int device);
+void photon_scene_destroy(photon_scene *s);
+
+/* Device image (float32 [ny*nx], accumulated onto). */
+int   photon_scene_zero_image(photon_scene *s);
+int   photon_scene_upload_image(photon_scene *s, const float *host_image);      /* H2D */
+int   photon_scene_download_image(photon_scene *s, float *host_image);          /* D2H, overwrites */
+void *photon_scene_image_device_ptr(photon_scene *s);                           /* for NCCL reduce by the caller */
+
+/*
+ * Trace all source points of the scene's shard onto the device image (replaces the
+ * launch loop prt.cu:3506-3559).  Asynchronous on the scene's stream; returns 0 on a
+ * successful launch.  photon_scene_sync waits and returns the CUDA status.
+ */
+int photon_scene_trace(photon_scene *s);
+int photon_scene_trace_range(photon_scene *s, int point_begin, int point_count);   /* shard-local points */
+int photon_scene_sync(photon_scene *s);
+
+/*
+ * Trace one dump batch (source points [batch*source_point_number, ...)) and copy the
+ * per-ray sensor positions and post-volume directions to host arrays of n_save float3
+ * (NaN where a ray was culled), as written to pos_%04d.bin / dir_%04d.bin by
+ * prt.cu:3561-3611.  inter_* may be NULL; otherwise n_save*n_inter float3 each.
+ */
+int photon_scene_trace_batch(photon_scene *s, int batch, long long n_save, float *final_pos, float *final_dir,
+                             int n_inter, float *inter_pos, float *inter_dir);
+
+/* Counters of the work done since the last photon_scene_reset_counters. */
+int       photon_scene_reset_counters(photon_scene *s);
+long long photon_scene_ray_steps(photon_scene *s);      /* committed integrator steps */
+long long photon_scene_rays(photon_scene *s);           /* rays generated */
+long long photon_scene_sensor_hits(photon_scene *s);    /* rays that reached the sensor */
+float     photon_scene_last_trace_ms(photon_scene *s);  /* CUDA-event time of the last trace */
+int       photon_scene_kernel_launches(photon_scene *s);/* kernels launched by the last trace */
+int       photon_scene_num_points(photon_scene *s);     /* source points in this shard */
+
+/* Field ingest alone (replaces trace.h:1663-2105): loads the NRRD, builds (grad n, n-1) on
+ * the GPU and copies it back.  meta16 = {min xyz, max xyz, spacing xyz, step, data_min, W, H, D, 0, 0}.
+ * out may be NULL to query the size. */
+int photon_b200_load_field(const char *path, float meta16[16], float *out_float4, long long capacity_voxels);
+
+/* FP32 FMA throughput of the device in TFLOP/s, measured with a register-resident FFMA loop
+ * (the roofline denominator for the trace kernel, which is FP32-issue bound, not HBM bound). */
+double photon_b200_measure_fp32_tflops(int device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PHOTON_B200_H_ */

@@ -19,6 +19,8 @@ def load_oracle(build=True):
     lib = ctypes.CDLL(so)
     lib.photon_oracle_last_ray_steps.restype = ctypes.c_longlong
     lib.photon_oracle_last_rays.restype = ctypes.c_longlong
+    lib.photon_oracle_last_trace_seconds.restype = ctypes.c_double
+    lib.photon_oracle_last_threads.restype = ctypes.c_int
     return lib
 
 

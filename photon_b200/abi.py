@@ -243,11 +243,11 @@ class RayTracingCall:
         esi = np.ascontiguousarray(self.element_system_index, np.int32)
         cam = camera_design_struct.from_buffer_copy(bytes(self.camera))
         args = (
-            C.c_float(self.lens_pitch), C.c_float(self.image_distance), C.byref(sc),
-            self.scattering_type.encode("utf-8"), C.byref(src),
+            C.c_float(self.lens_pitch), C.c_float(self.image_distance), C.pointer(sc),
+            self.scattering_type.encode("utf-8"), C.pointer(src),
             int(self.lightray_number_per_particle), C.c_float(self.beam_wavelength),
             C.c_float(self.aperture_f_number), ne, ec.ctypes.data, elems, ep.ctypes.data,
-            esi.ctypes.data, C.byref(cam), image.ctypes.data,
+            esi.ctypes.data, C.pointer(cam), image.ctypes.data,
             bool(self.simulate_density_gradients), self.density_grad_filename.encode("utf-8"),
             bool(self.save_lightrays), self.lightray_position_save_path.encode("utf-8"),
             self.lightray_direction_save_path.encode("utf-8"), int(self.num_lightrays_save),

@@ -1,0 +1,643 @@
+// driver.cu -- host side of libparallel_ray_tracing.so (B200 build).
+//
+// Replaces cuda_codes/parallel_ray_tracing.cu:3078-3775 (start_ray_tracing) and the field
+// setup of cuda_codes/trace_rays_through_density_gradients.h:1612-2105.  Differences in
+// structure (not in results): one stream, asynchronous uploads from the caller's buffers,
+// the density field is built on the GPU and cached across calls, all source points go
+// through one persistent launch unless ray dumps force the reference's per-batch files,
+// every CUDA call is checked, and nothing ever calls exit() inside the host process.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/stat.h>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/photon_b200.h"
+#include "nrrd_reader.h"
+#include "scene_args.h"
+#include "trace_kernel.cuh"
+
+using namespace ph;
+
+namespace {
+
+thread_local std::string g_error;
+bool verbose() { static int v = getenv("PHOTON_VERBOSE") ? atoi(getenv("PHOTON_VERBOSE")) : 0; return v != 0; }
+#define VLOG(...) do { if (verbose()) { printf(__VA_ARGS__); fflush(stdout); } } while (0)
+
+bool cuda_ok(cudaError_t e, const char *what, const char *file, int line) {
+    if (e == cudaSuccess) return true;
+    char buf[512];
+    snprintf(buf, sizeof buf, "%s failed: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
+    g_error = buf;
+    fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", buf);
+    return false;
+}
+#define CK(x) do { if (!cuda_ok((x), #x, __FILE__, __LINE__)) return false; } while (0)
+
+// ---------------------------------------------------------------------------------
+// Density field resident on one device; cached across calls (the BOS script calls the
+// library twice per run and the reference reloads + recomputes the field each time).
+// ---------------------------------------------------------------------------------
+struct DeviceField {
+    int device = -1;
+    std::string path; long long mtime = 0, fsize = 0;
+    FieldParams P{};
+    f3 spacing{};
+    f4 *lin = nullptr;                   // [D][H][W] float4 (grad n, n-1)
+    cudaArray_t arr = nullptr;           // optional 3-D array for the texture path
+    cudaTextureObject_t tex = 0;
+    void release() {
+        if (device >= 0) cudaSetDevice(device);
+        if (tex) cudaDestroyTextureObject(tex);
+        if (arr) cudaFreeArray(arr);
+        if (lin) cudaFree(lin);
+        tex = 0; arr = nullptr; lin = nullptr; device = -1; path.clear();
+    }
+};
+std::mutex g_field_mutex;
+std::vector<DeviceField *> g_fields;     // one cache entry per device
+
+bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) {
+    pnrrd::Volume vol;
+    if (!pnrrd::load(path, vol)) {
+        g_error = std::string("failed to load \"") + path + "\": " + vol.error;
+        fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
+        return false;
+    }
+    int sx = vol.nx, sy = vol.ny, sz = vol.nz;
+    // bounds from the header (trace.h:1698-1706); NRRD z origin is shifted by -750e3
+    double xmin = vol.origin[0], dx = vol.spacing[0], xmax = xmin + (sx - 1) * dx;
+    double ymin = vol.origin[1], dy = vol.spacing[1], ymax = ymin + (sy - 1) * dy;
+    double zmin = vol.origin[2] - 750e3, dz = vol.spacing[2], zmax = zmin + (sz - 1) * dz;
+    // the reference keeps at most 1024 planes (data_max = 1024, trace.h:2037-2038, 1713-1716)
+    // while the bounds keep the full extent; PHOTON_FULL_DEPTH=1 lifts the cut.
+    if (sz > 1024 && !getenv("PHOTON_FULL_DEPTH")) sz = 1024;
+    FieldParams P{};
+    P.mn = mk3((float)xmin, (float)ymin, (float)zmin);
+    P.mx = mk3((float)xmax, (float)ymax, (float)zmax);
+    P.scale = mk3(1.0f / (P.mx.x - P.mn.x), 1.0f / (P.mx.y - P.mn.y), 1.0f / (P.mx.z - P.mn.z));
+    P.W = sx; P.H = sy; P.D = sz;
+    P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
+    float step = (float)fmin(dx, dy);
+    step = step < dz ? step : (float)dz;
+    P.step = step;
+    size_t n = (size_t)sx * sy * sz;
+    float *d_rho = nullptr; unsigned int *d_min = nullptr;
+    CK(cudaMalloc(&d_rho, n * sizeof(float)));
+    CK(cudaMalloc(&F.lin, n * sizeof(f4)));
+    CK(cudaMalloc(&d_min, sizeof(unsigned int)));
+    CK(cudaMemcpyAsync(d_rho, vol.rho.data(), n * sizeof(float), cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(d_min, 0xff, sizeof(unsigned int), st));
+    int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)148 * 16);
+    build_field_kernel<<<blocks, 256, 0, st>>>(d_rho, F.lin, sx, sy, sz, (float)dx, (float)dy, (float)dz, d_min);
+    CK(cudaGetLastError());
+    unsigned int key = 0;
+    CK(cudaMemcpyAsync(&key, d_min, sizeof key, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    cudaFree(d_rho); cudaFree(d_min);
+    P.data_min = float_from_order_key(key);
+    P.skip_step = P.step / (1 + P.data_min);
+    F.P = P; F.device = device; F.path = path; F.spacing = mk3((float)dx, (float)dy, (float)dz);
+    VLOG("field %s: %d x %d x %d, step %.4f um, min(n-1) %.6g\n", path, sx, sy, sz, P.step, P.data_min);
+    return true;
+}
+
+bool ensure_texture(DeviceField &F, cudaStream_t st) {
+    if (F.tex) return true;
+    cudaChannelFormatDesc desc = cudaCreateChannelDesc<float4>();
+    cudaExtent ext = make_cudaExtent(F.P.W, F.P.H, F.P.D);
+    CK(cudaMalloc3DArray(&F.arr, &desc, ext));
+    cudaMemcpy3DParms cp = {};
+    cp.srcPtr = make_cudaPitchedPtr((void *)F.lin, (size_t)F.P.W * sizeof(float4), F.P.W, F.P.H);
+    cp.dstArray = F.arr; cp.extent = ext; cp.kind = cudaMemcpyDeviceToDevice;
+    CK(cudaMemcpy3DAsync(&cp, st));
+    cudaResourceDesc rd = {}; rd.resType = cudaResourceTypeArray; rd.res.array.array = F.arr;
+    cudaTextureDesc td = {};                                             // trace.h:1628-1631
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+    CK(cudaCreateTextureObject(&F.tex, &rd, &td, nullptr));
+    CK(cudaStreamSynchronize(st));
+    return true;
+}
+
+DeviceField *get_field(const char *path, int device, cudaStream_t st) {
+    struct stat sb;
+    long long mt = 0, fs = 0;
+    if (stat(path, &sb) == 0) { mt = (long long)sb.st_mtim.tv_sec * 1000000000LL + sb.st_mtim.tv_nsec; fs = (long long)sb.st_size; }
+    std::lock_guard<std::mutex> lk(g_field_mutex);
+    DeviceField *slot = nullptr;
+    for (auto *f : g_fields) if (f->device == device) slot = f;
+    if (slot && slot->path == path && slot->mtime == mt && slot->fsize == fs && !getenv("PHOTON_NO_FIELD_CACHE")) return slot;
+    if (slot) slot->release(); else { slot = new DeviceField(); g_fields.push_back(slot); }
+    if (!build_field(*slot, path, device, st)) { slot->release(); return nullptr; }
+    slot->mtime = mt; slot->fsize = fs;
+    return slot;
+}
+
+template <class T>
+bool upload(T *&dst, const T *src, size_t n, cudaStream_t st) {
+    dst = nullptr;
+    if (n == 0) return true;
+    CK(cudaMalloc(&dst, n * sizeof(T)));
+    CK(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+    return true;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------
+// A scene resident on one device
+// ---------------------------------------------------------------------------------
+struct photon_scene {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    TraceArgs args{};
+    DeviceField *field = nullptr;
+    bool use_texture = false;
+    int npoints = 0, point_offset = 0;   // shard of the caller's source points
+    int total_points = 0, source_point_number = 0;
+    float *d_sx = nullptr, *d_sy = nullptr, *d_sz = nullptr; double *d_srad = nullptr; int *d_sdiam = nullptr;
+    float *d_angle = nullptr, *d_irr = nullptr;
+    f2 *d_aim = nullptr;
+    float *d_image = nullptr;
+    unsigned long long *d_counters = nullptr;
+    unsigned long long h_counters[2] = {0, 0};
+    long long rays_traced = 0;
+    float last_ms = 0.0f;
+    int last_launches = 0, total_launches = 0;
+    int grid_blocks = 0;
+};
+
+namespace {
+
+int pick_device(int requested) {
+    if (requested >= 0) return requested;
+    if (const char *e = getenv("PHOTON_DEVICE")) return atoi(e);
+    int cur = 0;
+    if (cudaGetDevice(&cur) != cudaSuccess) cur = 0;
+    return cur;
+}
+
+bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_base,
+                  f3 *fpos, f3 *fdir, long long n_save, f3 *ipos, f3 *idir, int n_inter) {
+    if (point_count <= 0) return true;
+    TraceArgs a = s->args;
+    a.point_begin = point_begin; a.point_count = point_count; a.dump_point_base = dump_base;
+    a.final_pos = fpos; a.final_dir = fdir; a.n_save = n_save;
+    a.inter_pos = ipos; a.inter_dir = idir; a.n_inter = n_inter;
+    int grid = std::min(point_count, s->grid_blocks);
+    if (s->use_texture) {
+        TextureField S; S.tex = s->field->tex;
+        trace_rays_kernel<TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+    } else {
+        LinearField S; S.g = s->field ? s->field->lin : nullptr;
+        S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
+        trace_rays_kernel<LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+    }
+    CK(cudaGetLastError());
+    s->last_launches++; s->total_launches++;
+    s->rays_traced += (long long)point_count * a.rpp;
+    return true;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------
+// Extended C ABI (include/photon_b200.h)
+// ---------------------------------------------------------------------------------
+extern "C" {
+
+int photon_b200_abi_version(void) { return 1; }
+
+int photon_b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char *photon_b200_last_error(void) { return g_error.c_str(); }
+
+static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
+                       const scattering_data_t *sc, const char *scattering_type_str,
+                       const lightfield_source_t *src, int rpp, float beam_wavelength, float f_number,
+                       int ne, const double (*element_center)[3], const element_data_t *element_data,
+                       const double (*element_plane_parameters)[4], const int *element_system_index,
+                       const camera_design_t *cam, bool simulate_density_gradients, const char *density_grad_filename,
+                       int algorithm, bool add_pos_noise, float pos_noise_std, bool add_ngrad_noise,
+                       float ngrad_noise_std, float cone_ratio, int shard_index, int shard_count) {
+    CK(cudaSetDevice(s->device));
+    CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&s->ev0));
+    CK(cudaEventCreate(&s->ev1));
+    TraceArgs &a = s->args;
+    memset(&a, 0, sizeof a);
+    if (ne < 1 || ne > PH_MAX_ELEMENTS) { g_error = "num_elements must be in [1, 8]"; return false; }
+    if (rpp < 1) { g_error = "lightray_number_per_particle must be >= 1"; return false; }
+
+    // ---- source points (shard) : prt.cu:3162-3180
+    int np = src->num_particles;
+    if (shard_count < 1) { shard_count = 1; shard_index = 0; }
+    long long b = (long long)np * shard_index / shard_count, e = (long long)np * (shard_index + 1) / shard_count;
+    s->total_points = np; s->point_offset = (int)b; s->npoints = (int)(e - b);
+    s->source_point_number = src->source_point_number;
+    size_t n = (size_t)s->npoints;
+    if (!upload(s->d_sx, src->x + b, n, s->stream) || !upload(s->d_sy, src->y + b, n, s->stream) ||
+        !upload(s->d_sz, src->z + b, n, s->stream) || !upload(s->d_srad, src->radiance + b, n, s->stream) ||
+        !upload(s->d_sdiam, src->diameter_index + b, n, s->stream)) return false;
+    a.sx = s->d_sx; a.sy = s->d_sy; a.sz = s->d_sz; a.sradiance = s->d_srad; a.sdiam = s->d_sdiam;
+    a.rpp = rpp; a.global_point_offset = s->point_offset;
+
+    // ---- Mie table : prt.cu:3192-3210
+    a.mie.enabled = strcmp(scattering_type_str, "mie") == 0;
+    if (a.mie.enabled) {
+        if (!upload(s->d_angle, sc->scattering_angle, (size_t)sc->num_angles, s->stream) ||
+            !upload(s->d_irr, sc->scattering_irradiance, (size_t)sc->num_angles * sc->num_diameters, s->stream)) return false;
+        memcpy(a.mie.inv_rot, sc->inverse_rotation_matrix, sizeof a.mie.inv_rot);
+        memcpy(a.mie.beam, sc->beam_propagation_vector, sizeof a.mie.beam);
+        a.mie.angle = s->d_angle; a.mie.irradiance = s->d_irr;
+        a.mie.num_angles = sc->num_angles; a.mie.num_diameters = sc->num_diameters;
+    }
+
+    // ---- scalar scene parameters, lens samples, optical train, camera (scene_args.h)
+    std::vector<f2> aim;
+    if (!fill_scene_args(a, aim, lens_pitch, image_distance, sc, scattering_type_str, src, rpp, beam_wavelength, f_number,
+                         ne, element_center, element_data, element_plane_parameters, element_system_index, cam,
+                         algorithm, add_pos_noise, pos_noise_std, add_ngrad_noise, ngrad_noise_std, cone_ratio, g_error))
+        return false;
+    if (!a.philox) {
+        if (!upload(s->d_aim, aim.data(), aim.size(), s->stream)) return false;
+        CK(cudaStreamSynchronize(s->stream));    // aim is a local buffer
+        a.aim = s->d_aim;
+    }
+    Camera &c = a.cam;
+
+    // ---- density field : prt.cu:3323-3357
+    a.simulate_gradients = simulate_density_gradients ? 1 : 0;
+    if (simulate_density_gradients) {
+        s->field = get_field(density_grad_filename, s->device, s->stream);
+        if (!s->field) return false;
+        a.field = s->field->P;
+        const char *smp = getenv("PHOTON_SAMPLER");
+        s->use_texture = smp && strcmp(smp, "texture") == 0;
+        if (s->use_texture && !ensure_texture(*s->field, s->stream)) return false;
+        if (algorithm == 3 || algorithm == 4)
+            fprintf(stderr, "libparallel_ray_tracing(b200): ray_tracing_algorithm %d (rk45/adams-bashforth) is not "
+                            "implemented yet; rays pass the volume undeflected\n", algorithm);
+    }
+
+    // ---- image + counters
+    CK(cudaMalloc(&s->d_image, (size_t)c.nx * c.ny * sizeof(float)));
+    CK(cudaMemsetAsync(s->d_image, 0, (size_t)c.nx * c.ny * sizeof(float), s->stream));
+    CK(cudaMalloc(&s->d_counters, 2 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(s->d_counters, 0, 2 * sizeof(unsigned long long), s->stream));
+    a.image = s->d_image; a.counters = s->d_counters;
+
+    // persistent grid: a multiple of the SM count (148 on B200), 2 CTAs resident per SM
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, s->device));
+    int mult = 2 * 4;
+    if (const char *g = getenv("PHOTON_GRID_MULT")) mult = std::max(1, atoi(g));
+    s->grid_blocks = prop.multiProcessorCount * mult;
+    CK(cudaStreamSynchronize(s->stream));
+    return true;
+}
+
+photon_scene *photon_scene_create(float lens_pitch, float image_distance,
+                                  const scattering_data_t *sc, const char *scattering_type_str,
+                                  const lightfield_source_t *src, int rpp, float beam_wavelength, float f_number,
+                                  int ne, const double (*element_center)[3], const element_data_t *element_data,
+                                  const double (*element_plane_parameters)[4], const int *element_system_index,
+                                  const camera_design_t *cam, bool simulate_density_gradients,
+                                  const char *density_grad_filename, int algorithm, bool add_pos_noise,
+                                  float pos_noise_std, bool add_ngrad_noise, float ngrad_noise_std, float cone_ratio,
+                                  int shard_index, int shard_count, int device) {
+    g_error.clear();
+    if (photon_b200_device_count() < 1) {
+        g_error = "no CUDA device available (this library has no CPU path)";
+        fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
+        return nullptr;
+    }
+    photon_scene *s = new photon_scene();
+    s->device = pick_device(device);
+    if (!scene_fill(s, lens_pitch, image_distance, sc, scattering_type_str, src, rpp, beam_wavelength, f_number, ne,
+                    element_center, element_data, element_plane_parameters, element_system_index, cam,
+                    simulate_density_gradients, density_grad_filename, algorithm, add_pos_noise, pos_noise_std,
+                    add_ngrad_noise, ngrad_noise_std, cone_ratio, shard_index, shard_count)) {
+        if (!g_error.empty()) fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
+        photon_scene_destroy(s);
+        return nullptr;
+    }
+    return s;
+}
+
+void photon_scene_destroy(photon_scene *s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    cudaFree(s->d_sx); cudaFree(s->d_sy); cudaFree(s->d_sz); cudaFree(s->d_srad); cudaFree(s->d_sdiam);
+    cudaFree(s->d_angle); cudaFree(s->d_irr); cudaFree(s->d_aim); cudaFree(s->d_image); cudaFree(s->d_counters);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;   // the field stays in the per-device cache
+}
+
+static bool scene_ok(photon_scene *s) { if (!s) { g_error = "null scene"; return false; } return cudaSetDevice(s->device) == cudaSuccess; }
+
+int photon_scene_zero_image(photon_scene *s) {
+    if (!scene_ok(s)) return 1;
+    return cuda_ok(cudaMemsetAsync(s->d_image, 0, (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float), s->stream),
+                   "zero image", __FILE__, __LINE__) ? 0 : 1;
+}
+int photon_scene_upload_image(photon_scene *s, const float *h) {
+    if (!scene_ok(s)) return 1;
+    return cuda_ok(cudaMemcpyAsync(s->d_image, h, (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float),
+                                   cudaMemcpyHostToDevice, s->stream), "image H2D", __FILE__, __LINE__) ? 0 : 1;
+}
+int photon_scene_download_image(photon_scene *s, float *h) {
+    if (!scene_ok(s)) return 1;
+    if (!cuda_ok(cudaMemcpyAsync(h, s->d_image, (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float),
+                                 cudaMemcpyDeviceToHost, s->stream), "image D2H", __FILE__, __LINE__)) return 1;
+    return cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__) ? 0 : 1;
+}
+void *photon_scene_image_device_ptr(photon_scene *s) { return s ? (void *)s->d_image : nullptr; }
+
+int photon_scene_trace(photon_scene *s) {
+    if (!scene_ok(s)) return 1;
+    s->last_launches = 0;
+    if (!cuda_ok(cudaEventRecord(s->ev0, s->stream), "event", __FILE__, __LINE__)) return 1;
+    if (!launch_trace(s, 0, s->npoints, 0, nullptr, nullptr, 0, nullptr, nullptr, 0)) return 1;
+    if (!cuda_ok(cudaEventRecord(s->ev1, s->stream), "event", __FILE__, __LINE__)) return 1;
+    return 0;
+}
+
+int photon_scene_trace_range(photon_scene *s, int point_begin, int point_count) {
+    if (!scene_ok(s)) return 1;
+    if (point_begin < 0 || point_count < 0 || point_begin + point_count > s->npoints) { g_error = "point range outside the shard"; return 1; }
+    s->last_launches = 0;
+    if (!cuda_ok(cudaEventRecord(s->ev0, s->stream), "event", __FILE__, __LINE__)) return 1;
+    if (!launch_trace(s, point_begin, point_count, point_begin, nullptr, nullptr, 0, nullptr, nullptr, 0)) return 1;
+    if (!cuda_ok(cudaEventRecord(s->ev1, s->stream), "event", __FILE__, __LINE__)) return 1;
+    return 0;
+}
+
+int photon_scene_sync(photon_scene *s) {
+    if (!scene_ok(s)) return 1;
+    if (!cuda_ok(cudaStreamSynchronize(s->stream), "trace kernel", __FILE__, __LINE__)) return 1;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) s->last_ms = ms; else cudaGetLastError();
+    return 0;
+}
+
+int photon_scene_trace_batch(photon_scene *s, int batch, long long n_save, float *final_pos, float *final_dir,
+                             int n_inter, float *inter_pos, float *inter_dir) {
+    if (!scene_ok(s)) return 1;
+    int spn = s->source_point_number;
+    if (s->npoints < spn) spn = s->npoints;                              // prt.cu:3366-3368
+    if (spn <= 0) return 0;
+    int begin = batch * spn, count = std::min(spn, s->npoints - begin);
+    if (count <= 0 || n_save < 0) return 0;
+    f3 *dpos = nullptr, *ddir = nullptr, *dipos = nullptr, *didir = nullptr;
+    bool ok = true;
+    size_t nb = (size_t)n_save * sizeof(f3), nib = nb * (size_t)std::max(n_inter, 0);
+    const bool inter = s->args.simulate_gradients && n_inter > 0 && inter_pos && inter_dir && n_save > 0;
+    auto fail = [&]() { cudaFree(dpos); cudaFree(ddir); cudaFree(dipos); cudaFree(didir); return 1; };
+    if (n_save > 0) {
+        ok = cuda_ok(cudaMalloc(&dpos, nb), "dump alloc", __FILE__, __LINE__) && cuda_ok(cudaMalloc(&ddir, nb), "dump alloc", __FILE__, __LINE__);
+        if (!ok) return fail();
+        cudaMemsetAsync(dpos, 0xff, nb, s->stream); cudaMemsetAsync(ddir, 0xff, nb, s->stream);   // all-ones = NaN (prt.cu:3527-3533)
+    }
+    if (inter) {
+        ok = cuda_ok(cudaMalloc(&dipos, nib), "dump alloc", __FILE__, __LINE__) && cuda_ok(cudaMalloc(&didir, nib), "dump alloc", __FILE__, __LINE__);
+        if (!ok) return fail();
+        cudaMemsetAsync(dipos, 0xff, nib, s->stream); cudaMemsetAsync(didir, 0xff, nib, s->stream);
+    }
+    s->last_launches = 0;
+    cudaEventRecord(s->ev0, s->stream);
+    if (!launch_trace(s, begin, count, begin, dpos, ddir, n_save, dipos, didir, inter ? n_inter : 0)) return fail();
+    cudaEventRecord(s->ev1, s->stream);
+    if (n_save > 0 && final_pos) cudaMemcpyAsync(final_pos, dpos, nb, cudaMemcpyDeviceToHost, s->stream);
+    if (n_save > 0 && final_dir) cudaMemcpyAsync(final_dir, ddir, nb, cudaMemcpyDeviceToHost, s->stream);
+    if (inter) {
+        cudaMemcpyAsync(inter_pos, dipos, nib, cudaMemcpyDeviceToHost, s->stream);
+        cudaMemcpyAsync(inter_dir, didir, nib, cudaMemcpyDeviceToHost, s->stream);
+    }
+    int rc = photon_scene_sync(s);
+    cudaFree(dpos); cudaFree(ddir); cudaFree(dipos); cudaFree(didir);
+    return rc;
+}
+
+static bool fetch_counters(photon_scene *s) {
+    if (!scene_ok(s)) return false;
+    CK(cudaMemcpyAsync(s->h_counters, s->d_counters, sizeof s->h_counters, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    return true;
+}
+int photon_scene_reset_counters(photon_scene *s) {
+    if (!scene_ok(s)) return 1;
+    s->rays_traced = 0; s->total_launches = 0;
+    return cuda_ok(cudaMemsetAsync(s->d_counters, 0, 2 * sizeof(unsigned long long), s->stream), "reset", __FILE__, __LINE__) ? 0 : 1;
+}
+long long photon_scene_ray_steps(photon_scene *s) { return fetch_counters(s) ? (long long)s->h_counters[0] : -1; }
+long long photon_scene_sensor_hits(photon_scene *s) { return fetch_counters(s) ? (long long)s->h_counters[1] : -1; }
+long long photon_scene_rays(photon_scene *s) { return s ? s->rays_traced : -1; }
+float photon_scene_last_trace_ms(photon_scene *s) { return s ? s->last_ms : -1.0f; }
+int photon_scene_kernel_launches(photon_scene *s) { return s ? s->last_launches : -1; }
+int photon_scene_num_points(photon_scene *s) { return s ? s->npoints : -1; }
+
+int photon_b200_load_field(const char *path, float meta16[16], float *out, long long capacity_voxels) {
+    g_error.clear();
+    if (photon_b200_device_count() < 1) { g_error = "no CUDA device available"; return 1; }
+    int dev = pick_device(-1);
+    if (cudaSetDevice(dev) != cudaSuccess) return 1;
+    cudaStream_t st;
+    if (cudaStreamCreate(&st) != cudaSuccess) return 1;
+    DeviceField *F = get_field(path, dev, st);
+    int rc = 1;
+    if (F) {
+        const FieldParams &P = F->P;
+        float m[16] = {P.mn.x, P.mn.y, P.mn.z, P.mx.x, P.mx.y, P.mx.z, 0, 0, 0, P.step, P.data_min,
+                       (float)P.W, (float)P.H, (float)P.D, 0, 0};
+        m[6] = F->spacing.x; m[7] = F->spacing.y; m[8] = F->spacing.z;
+        memcpy(meta16, m, sizeof m);
+        size_t n = (size_t)P.W * P.H * P.D;
+        rc = 0;
+        if (out && capacity_voxels >= (long long)n)
+            rc = cudaMemcpy(out, F->lin, n * sizeof(f4), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
+    }
+    cudaStreamDestroy(st);
+    return rc;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------
+// The entry point photon's Python binds (include/photon_abi.h)
+// ---------------------------------------------------------------------------------
+namespace {
+
+bool write_f3_file(const std::string &dir, const char *prefix, int k, const float *data, size_t count_f3) {
+    char name[64];
+    snprintf(name, sizeof name, "/%s%04d.bin", prefix, k);               // prt.cu:3566-3571
+    std::string path = dir + name;
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) { fprintf(stderr, "libparallel_ray_tracing(b200): cannot write %s\n", path.c_str()); return false; }
+    fwrite(data, 3 * sizeof(float), count_f3, f);
+    fclose(f);
+    return true;
+}
+
+struct ShardResult { bool ok = false; std::vector<float> image; long long steps = 0, rays = 0; float ms = 0; };
+
+}  // namespace
+
+extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
+                                  scattering_data_t *scattering_data_p, char *scattering_type_str,
+                                  lightfield_source_t *lightfield_source_p, int lightray_number_per_particle,
+                                  float beam_wavelength, float aperture_f_number,
+                                  int num_elements, double (*element_center)[3], element_data_t *element_data_p,
+                                  double (*element_plane_parameters)[4], int *element_system_index,
+                                  camera_design_t *camera_design_p, float *image_array,
+                                  bool simulate_density_gradients, char *density_grad_filename,
+                                  bool save_lightrays, char *lightray_position_save_path,
+                                  char *lightray_direction_save_path,
+                                  int num_lightrays_save, int ray_tracing_algorithm,
+                                  bool add_pos_noise, float pos_noise_std,
+                                  bool add_ngrad_noise, float ngrad_noise_std,
+                                  float ray_cone_pitch_ratio,
+                                  bool save_intermediate_ray_data, int num_intermediate_positions_save) {
+    g_error.clear();
+    const int np = lightfield_source_p->num_particles;
+    VLOG("number of particles: %d\n", np);
+    int shard_index = 0, shard_count = 1;
+    if (const char *sh = getenv("PHOTON_SHARD")) {
+        if (sscanf(sh, "%d/%d", &shard_index, &shard_count) != 2 || shard_count < 1 || shard_index < 0 || shard_index >= shard_count) {
+            fprintf(stderr, "libparallel_ray_tracing(b200): bad PHOTON_SHARD \"%s\" (want r/n)\n", sh);
+            return;
+        }
+    }
+    int ngpus = 1;
+    if (const char *g = getenv("PHOTON_GPUS")) ngpus = std::max(1, std::min(atoi(g), photon_b200_device_count()));
+    const bool dumps = save_lightrays && num_lightrays_save > 0;
+    const bool inter = simulate_density_gradients && save_intermediate_ray_data && num_intermediate_positions_save > 0 && num_lightrays_save > 0;
+    if (dumps || inter) ngpus = 1;       // dump files are per batch of the whole point list
+    const size_t npix = (size_t)camera_design_p->x_pixel_number * camera_design_p->y_pixel_number;
+
+    auto make_scene = [&](int si, int sc, int dev) {
+        return photon_scene_create(lens_pitch, image_distance, scattering_data_p, scattering_type_str, lightfield_source_p,
+                                   lightray_number_per_particle, beam_wavelength, aperture_f_number, num_elements,
+                                   element_center, element_data_p, element_plane_parameters, element_system_index,
+                                   camera_design_p, simulate_density_gradients, density_grad_filename, ray_tracing_algorithm,
+                                   add_pos_noise, pos_noise_std, add_ngrad_noise, ngrad_noise_std, ray_cone_pitch_ratio,
+                                   si, sc, dev);
+    };
+
+    if (ngpus == 1) {
+        photon_scene *s = make_scene(shard_index, shard_count, -1);
+        if (!s) return;                                                  // image untouched
+        bool ok = photon_scene_upload_image(s, image_array) == 0;        // accumulate onto the caller's image (prt.cu:3309)
+        if (ok && (dumps || inter)) {
+            int spn = std::min(lightfield_source_p->source_point_number, np);
+            int kmax = spn > 0 ? (np + spn - 1) / spn : 0;               // prt.cu:3506-3510
+            size_t ns = (size_t)std::max(num_lightrays_save, 0);
+            std::vector<float> fpos(3 * ns), fdir(3 * ns), ipos, idir;
+            if (inter) { ipos.resize(3 * ns * num_intermediate_positions_save); idir.resize(ipos.size()); }
+            for (int k = 0; k < kmax && ok; k++) {
+                VLOG("%d out of %d\n", k + 1, kmax);
+                ok = photon_scene_trace_batch(s, k, (long long)ns, fpos.data(), fdir.data(),
+                                              inter ? num_intermediate_positions_save : 0,
+                                              inter ? ipos.data() : nullptr, inter ? idir.data() : nullptr) == 0;
+                if (ok && dumps) {
+                    write_f3_file(lightray_position_save_path, "pos_", k, fpos.data(), ns);
+                    write_f3_file(lightray_direction_save_path, "dir_", k, fdir.data(), ns);
+                }
+                if (ok && inter) {                                       // prt.cu:3613-3670
+                    write_f3_file(lightray_position_save_path, "intermediate_pos_", k, ipos.data(), ns * num_intermediate_positions_save);
+                    write_f3_file(lightray_direction_save_path, "intermediate_dir_", k, idir.data(), ns * num_intermediate_positions_save);
+                }
+            }
+        } else if (ok) {
+            ok = photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
+        }
+        if (ok) {
+            std::vector<float> tmp(npix);
+            if (photon_scene_download_image(s, tmp.data()) == 0) memcpy(image_array, tmp.data(), npix * sizeof(float));
+            VLOG("traced %lld rays, %lld ray-steps, kernel %.3f ms\n", photon_scene_rays(s), photon_scene_ray_steps(s), photon_scene_last_trace_ms(s));
+        }
+        photon_scene_destroy(s);
+        return;
+    }
+
+    // ---- several GPUs inside one call: contiguous source-point shards, field replicated per
+    // GPU, private images, one sum at the end.  One host thread per device.
+    std::vector<ShardResult> res((size_t)ngpus);
+    std::vector<std::thread> th;
+    for (int g = 0; g < ngpus; g++) {
+        th.emplace_back([&, g]() {
+            photon_scene *s = make_scene(shard_index * ngpus + g, shard_count * ngpus, g);
+            if (!s) return;
+            res[g].image.resize(npix);
+            res[g].ok = photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0 &&
+                        photon_scene_download_image(s, res[g].image.data()) == 0;
+            photon_scene_destroy(s);
+        });
+    }
+    for (auto &t : th) t.join();
+    for (int g = 0; g < ngpus; g++) if (!res[g].ok) { fprintf(stderr, "libparallel_ray_tracing(b200): GPU %d failed; image untouched\n", g); return; }
+    for (size_t i = 0; i < npix; i++) {
+        float acc = image_array[i];
+        for (int g = 0; g < ngpus; g++) acc += res[g].image[i];
+        image_array[i] = acc;
+    }
+}
+
+// ---------------------------------------------------------------------------------
+// Roofline denominator measured on the box: FP32 FMA issue rate (the tracer is bound by
+// FP32 issue / L1 latency, not by HBM; MEASURED_PEAKS.json only has HBM and bf16 figures).
+// ---------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float *out, int iters, float a, float b) {
+    float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+        }
+    }
+    float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 123.456f) out[0] = s;
+}
+}  // namespace
+
+extern "C" double photon_b200_measure_fp32_tflops(int device) {
+    if (photon_b200_device_count() < 1) return -1.0;
+    int dev = pick_device(device);
+    if (cudaSetDevice(dev) != cudaSuccess) return -1.0;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return -1.0;
+    float *d = nullptr;
+    if (cudaMalloc(&d, 4) != cudaSuccess) return -1.0;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int iters = 4096, blocks = prop.multiProcessorCount * 8, threads = 256;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(e0);
+        fp32_peak_kernel<<<blocks, threads>>>(d, iters, 0.999f, 0.001f);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        double flops = 2.0 * 8 * 16 * (double)iters * threads * blocks;
+        double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    return best;
+}

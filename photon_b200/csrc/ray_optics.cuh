@@ -1,0 +1,220 @@
+// ray_optics.cuh -- stage (c) optical train and stage (d) sensor projection + splat weights.
+// Included from ray_stages.cuh.
+#pragma once
+#include "vecmath.cuh"
+
+namespace ph {
+
+// prt.cu:239-343.  Quadratic in float, discriminant and roots through double
+// sub-expressions (the literals 4.0 and 2.0 promote).  Root choice: smaller root for
+// R > 0, larger for R <= 0, for both surfaces (prt.cu:298-336).
+PH_HD f3 ray_sphere(f3 c, float R, f3 d, f3 p) {
+    float alpha = dot_rn(d, d);
+    f3 pc = p - c;
+    float beta = 2 * dot_rn(d, pc);
+    float gamma = add_rn(dot_rn(pc, pc), -mul_rn(R, R));
+    float disc = (float)((double)(beta * beta) - 4.0 * (double)alpha * (double)gamma);
+    if (disc < 0.0f) return nan3();
+    float sq = sqrtf(disc);
+    double den = 2.0 * (double)alpha;
+    float t1 = (float)((double)(-beta + sq) / den);
+    float t2 = (float)((double)(-beta - sq) / den);
+    float t = (R > 0) ? (t1 <= t2 ? t1 : t2) : (t1 >= t2 ? t1 : t2);
+    return p + d * t;
+}
+
+// prt.cu:345-380
+PH_HD float axis_distance(f3 p, f3 c, f4 pl) {
+    f3 n = mk3(pl.x, pl.y, pl.z);
+    float tmin = dot(n, p - c) / (pl.x * pl.x + pl.y * pl.y + pl.z * pl.z);
+    f3 q = c + n * tmin;
+    f3 e = p - q;
+    return sqrtf(dot(e, e));
+}
+
+// Cauchy dispersion with the Abbe number (prt.cu:622-636 front, 774-784 back).
+PH_HD double dispersed_index(double n_glass, float abbe, float wavelength, bool front) {
+    const float lD = 589.3f, lF = 486.1f, lC = 656.3f;
+    double inv_l2 = 1.0 / (double)(wavelength * wavelength);
+    double inv_d2 = front ? (double)(1 / (lD * lD)) : 1.0 / (double)(lD * lD);
+    return n_glass + (inv_l2 - inv_d2) * ((n_glass - 1) / (double)(abbe * (1 / (lF * lF) - 1 / (lC * lC))));
+}
+
+// Snell at a surface with unit normal N facing the incoming ray; eta = n_in/n_out
+// (prt.cu:655-690).  Returns false on total internal reflection.
+PH_HD bool refract(f3 &dir, f3 N, float eta) {
+    float cosi = -dot(dir, N);
+    float rad = (float)(1.0 - (double)(eta * eta) * (1.0 - (double)(cosi * cosi)));
+    if (rad < 0.0f) return false;
+    dir = dir * eta + (eta * cosi - sqrtf(rad)) * N;
+    dir = normalize(dir);
+    return true;
+}
+
+// prt.cu:383-1011
+PH_HD void refract_element(const Element &el, Ray &ray) {
+    f3 dir = ray.dir, pos = ray.pos;
+    f4 pl = el.plane;
+    f3 n = mk3(pl.x, pl.y, pl.z);
+    const double half_pitch = (double)el.pitch / 2.0;
+    if (el.type == 't') {
+        float t = -(dot(n, pos) + pl.w) / dot(n, dir);
+        f3 hit = pos + dir * t;
+        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        pos = hit;
+        dir = normalize(-(pos - el.centre) / el.focal + dir);            // prt.cu:494-496
+    } else if (el.type == 'l') {
+        float nmag = sqrtf(pl.x * pl.x + pl.y * pl.y + pl.z * pl.z);
+        float ds = (float)(el.vertex / 2.0 - (double)el.r_front);        // prt.cu:551
+        f3 cf = el.centre + n * ds / nmag;
+        f3 hit = ray_sphere(cf, el.r_front, dir, pos);
+        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        f3 N = normalize(hit - cf);
+        float eta = is_nan(el.abbe) ? (float)(1.0 / el.n_glass)
+                                    : (float)(1.0 / dispersed_index(el.n_glass, el.abbe, ray.wavelength, true));
+        if (!refract(dir, N, eta)) { kill(ray); return; }
+        pos = hit;
+        ds = (float)(-el.vertex / 2 - (double)el.r_back);                // prt.cu:714
+        f3 cb = el.centre + n * ds / nmag;
+        hit = ray_sphere(cb, el.r_back, dir, pos);
+        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        N = normalize(-(hit - cb));
+        eta = is_nan(el.abbe) ? (float)el.n_glass : (float)dispersed_index(el.n_glass, el.abbe, ray.wavelength, false);
+        if (!refract(dir, N, eta)) { kill(ray); return; }
+        if (el.absorbance != 0) {                                        // prt.cu:838-853
+            f3 e = hit - pos;
+            float dist = sqrtf(dot(e, e));
+            ray.radiance = (1.0 - (double)el.absorbance) * ray.radiance * (double)dist;
+        } else ray.radiance = (double)el.transmission * ray.radiance;
+        pos = hit;
+    } else {                                                             // aperture, prt.cu:868-992
+        float nmag = sqrtf(pl.x * pl.x + pl.y * pl.y + pl.z * pl.z);
+        float ds = (float)(-el.vertex / 2.0);
+        float dtmp = pl.w - ds * nmag;
+        float t = -(dot(n, pos) + dtmp) / dot(n, dir);
+        f3 hit = pos + dir * t;
+        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        ds = (float)(el.vertex / 2);
+        dtmp = pl.w - ds * nmag;
+        t = -(dot(n, pos) + dtmp) / dot(n, dir);
+        hit = pos + dir * t;
+        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        pos = hit;
+    }
+    ray.dir = dir; ray.pos = pos;
+}
+
+// prt.cu:1274-1381 with the intended element-per-stage order (deviation B-3).
+PH_HD void optical_train(const OpticalTrain &ot, Ray &ray) {
+    for (int s = 0; s < ot.stages; s++) {
+        int e = ot.order[s];
+        if (e < 0) continue;
+        refract_element(ot.e[e], ray);
+        if (any_nan(ray.pos) || any_nan(ray.dir)) return;
+    }
+}
+
+// ----------------------------------------------------------------------------------
+// (d) sensor
+// ----------------------------------------------------------------------------------
+PH_HD f3 sensor_plane_hit(const Ray &ray, const Camera &cam) {          // prt.cu:1403-1415
+    f3 nrm = mk3(0.0f, 0.0f, 1.0f);
+    float t = -(dot(nrm, ray.pos) + (-cam.z_sensor)) / dot(nrm, ray.dir);
+    return ray.pos + ray.dir * t;
+}
+PH_HD double cos4_alpha(f3 d) {                                         // prt.cu:1461-1463
+    float qx = d.x / d.z, qy = d.y / d.z;
+    float alpha = atanf(sqrtf(qx * qx + qy * qy));
+    float c = cosf(alpha);
+    return (double)(c * c * c * c);
+}
+
+// Separable erf-Gaussian footprint of one ray (prt.cu:1466-1540).  The reference
+// evaluates 4 erf per rendered pixel; ex depends only on the column and ey only on
+// the row, so evaluating them once per column/row gives bit-identical increments with
+// ~4x fewer erf calls.  PH_SPLAT_MAX bounds the footprint (ceil(1.5 D)+2 columns).
+#define PH_SPLAT_MAX 16
+struct ErfFootprint {
+    int c0, r0, nc, nr;        // first column/row and counts (unclipped)
+    float X, Y, radius;
+    double ex[PH_SPLAT_MAX], ey[PH_SPLAT_MAX];
+    double scale;              // peak*pi/32
+    bool valid;
+};
+
+PH_HD void erf_footprint(ErfFootprint &fp, float d_x, float d_y, double radiance, double c4,
+                         float diam, float frac) {
+    const double pi = 3.141592653589793;
+    fp.X = (float)((double)d_x - 0.5); fp.Y = (float)((double)d_y - 0.5);
+    float peak = (float)(radiance * c4 * 8.0 / pi);
+    float sqrt8 = sqrtf(8.0f);
+    fp.radius = frac * diam;
+    fp.c0 = (int)floorf(fp.X - fp.radius); int c1 = (int)ceilf(fp.X + fp.radius);
+    fp.r0 = (int)floorf(fp.Y - fp.radius); int r1 = (int)ceilf(fp.Y + fp.radius);
+    fp.nc = c1 - fp.c0 + 1; fp.nr = r1 - fp.r0 + 1;
+    fp.valid = fp.nc >= 1 && fp.nr >= 1 && fp.nc <= PH_SPLAT_MAX && fp.nr <= PH_SPLAT_MAX;
+    fp.scale = (double)peak * pi / 32.0;
+    if (!fp.valid) return;
+#pragma unroll 1
+    for (int i = 0; i < fp.nc; i++) {
+        double u = (double)((float)(fp.c0 + i) - fp.X);
+        fp.ex[i] = erf((double)sqrt8 * (u - 0.5) / (double)diam) - erf((double)sqrt8 * (u + 0.5) / (double)diam);
+    }
+#pragma unroll 1
+    for (int i = 0; i < fp.nr; i++) {
+        double u = (double)((float)(fp.r0 + i) - fp.Y);
+        fp.ey[i] = erf((double)sqrt8 * (u - 0.5) / (double)diam) - erf((double)sqrt8 * (u + 0.5) / (double)diam);
+    }
+}
+
+template <class Acc>
+PH_HD void erf_splat(const ErfFootprint &fp, const Camera &cam, Acc &acc) {
+    if (!fp.valid) return;
+    for (int i = 0; i < fp.nc; i++) {
+        int col = fp.c0 + i;
+        if (col < 0 || col > cam.nx - 1) continue;
+        float dx = (float)col - fp.X;
+        for (int j = 0; j < fp.nr; j++) {
+            int row = fp.r0 + j;
+            if (row < 0 || row > cam.ny - 1) continue;
+            float dy = (float)row - fp.Y;
+            float rr = sqrtf(dx * dx + dy * dy);
+            if (!(rr <= fp.radius)) continue;
+            float inc = (float)(fp.scale * fp.ex[i] * fp.ey[j]);
+            acc.add(row, col, inc);
+        }
+    }
+}
+
+// pixel coordinates of a sensor hit; flip_x for the diffraction / apparent models
+// (prt.cu:1446-1447) and not for the bilinear model (prt.cu:1807-1808).
+PH_HD bool pixel_coords(f3 hit, const Camera &cam, bool flip_x, float &d_x, float &d_y) {
+    float u = (hit.x - cam.p1x) / cam.pitch;
+    d_x = flip_x ? (float)(cam.nx - 1) - u : u;
+    d_y = (hit.y - cam.p1y) / cam.pitch;
+    return !(d_x >= cam.nx || d_y >= cam.ny || d_x < 0 || d_y < 0);
+}
+
+// Bilinear 4-pixel splat (prt.cu:1810-1850 weights, 2219-2234 accumulation).  The
+// reference subtracts 1 from both indices after its bounds test; a resulting negative
+// linear index (its out-of-bounds write) is dropped.
+template <class Acc>
+PH_HD void bilinear_splat(float d_x, float d_y, double radiance, double c4, const Camera &cam, Acc &acc) {
+    float yl = (float)((double)d_y - 0.5), xl = (float)((double)d_x - 0.5);
+    float cy = ceilf(yl), cx = ceilf(xl);
+    double dii = (double)(cy - yl), djj = (double)(cx - xl);
+    int ii0 = (int)(cy - 1), jj0 = (int)(cx - 1);
+    double rc = radiance;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        int ii = ii0 + (k >> 1), jj = jj0 + (k & 1);
+        double w = ((k >> 1) ? (1 - dii) : dii) * ((k & 1) ? (1 - djj) : djj);
+        if (ii < 0 || ii >= cam.ny || jj < 0 || jj >= cam.nx) continue;
+        long idx = (long)(ii - 1) * cam.nx + jj - 1;
+        if (idx < 0) continue;
+        float inc = (float)(w * rc * c4);
+        acc.add_linear(idx, inc);
+    }
+}
+
+}  // namespace ph
