@@ -3,8 +3,8 @@
 // The operation order is the one the reference's operator layer fixes
 // (CubicInterpolationCUDA/code/internal/cutil_math_bugfixes.h:302-409: a/s = a*(1/s),
 // normalize(v) = v*(1/sqrt(dot)), dot = x*x+y*y+z*z left to right), because sensor
-// positions are compared to 1e-3 px.  nvcc may contract mul+add into FMA; the parity
-// tests measure what that costs (it stays far inside the tolerance).
+// positions are compared to 1e-3 px.  FMA contraction is allowed only inside the integrator
+// loop (type q3 below); everything else rounds each operation on its own (type f3).
 //
 // Everything is __host__ __device__ so tests/hostcheck can run the same code on the CPU.
 #pragma once
@@ -21,22 +21,7 @@
 
 namespace ph {
 
-struct f3 { float x, y, z; };
-struct f4 { float x, y, z, w; };
-
-PH_HD f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
-PH_HD f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
-PH_HD f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
-PH_HD f3 operator-(f3 a) { return mk3(-a.x, -a.y, -a.z); }
-PH_HD f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
-PH_HD f3 operator*(float s, f3 a) { return mk3(a.x * s, a.y * s, a.z * s); }
-PH_HD f3 operator/(f3 a, float s) { float inv = 1.0f / s; return a * inv; }
-PH_HD float dot(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-PH_HD f3 normalize(f3 v) { float inv = 1.0f / sqrtf(dot(v, v)); return v * inv; }
-// Exactly rounded single operations that the compiler may not fuse into an FMA.  Used where
-// the reference's float arithmetic cancels catastrophically (ray-sphere quadratic at
-// |p-c| ~ 1e6 um, prt.cu:271-276), so that a fused multiply-add would move the sensor hit
-// by more than the 1e-3 px parity tolerance.
+// Exactly rounded single operations that the compiler may not fuse into an FMA.
 PH_HD float mul_rn(float a, float b) {
 #if defined(__CUDA_ARCH__)
     return __fmul_rn(a, b);
@@ -51,7 +36,38 @@ PH_HD float add_rn(float a, float b) {
     volatile float r = a + b; return r;
 #endif
 }
-PH_HD float dot_rn(f3 a, f3 b) { return add_rn(add_rn(mul_rn(a.x, b.x), mul_rn(a.y, b.y)), mul_rn(a.z, b.z)); }
+
+// Two flavours of the same 3-vector:
+//   f3 = v3<1>  every multiply and add is rounded on its own (no FMA contraction).  Used by the
+//               per-ray stages -- generation, frame rotations, lens, sensor -- whose float32
+//               arithmetic at |coordinates| ~ 1e6 um cancels catastrophically (ray-sphere
+//               quadratic prt.cu:271-276, plane hits), so that a fused multiply-add moves the
+//               sensor hit by more than the 1e-3 px parity tolerance.  The reference's debug
+//               build (-G -O0) does not contract either.
+//   q3 = v3<0>  plain operators that nvcc contracts into FFMA.  Used only inside the integrator
+//               loop (rk4_march / euler_march and the trilinear fetch), where the FP32 issue
+//               rate is the bound and the contraction error is ~1e-7 relative per step.
+template <int STRICT> struct v3 { float x, y, z; };
+typedef v3<1> f3;
+typedef v3<0> q3;
+struct f4 { float x, y, z, w; };
+
+template <int S> PH_HD float pmul(float a, float b) { return S ? mul_rn(a, b) : a * b; }
+template <int S> PH_HD float padd(float a, float b) { return S ? add_rn(a, b) : a + b; }
+
+template <int S> PH_HD v3<S> mkv(float x, float y, float z) { v3<S> r; r.x = x; r.y = y; r.z = z; return r; }
+PH_HD f3 mk3(float x, float y, float z) { return mkv<1>(x, y, z); }
+PH_HD q3 relax(f3 a) { return mkv<0>(a.x, a.y, a.z); }
+PH_HD f3 strict(q3 a) { return mkv<1>(a.x, a.y, a.z); }
+template <int S> PH_HD v3<S> operator+(v3<S> a, v3<S> b) { return mkv<S>(padd<S>(a.x, b.x), padd<S>(a.y, b.y), padd<S>(a.z, b.z)); }
+template <int S> PH_HD v3<S> operator-(v3<S> a, v3<S> b) { return mkv<S>(padd<S>(a.x, -b.x), padd<S>(a.y, -b.y), padd<S>(a.z, -b.z)); }
+template <int S> PH_HD v3<S> operator-(v3<S> a) { return mkv<S>(-a.x, -a.y, -a.z); }
+template <int S> PH_HD v3<S> operator*(v3<S> a, float s) { return mkv<S>(pmul<S>(a.x, s), pmul<S>(a.y, s), pmul<S>(a.z, s)); }
+template <int S> PH_HD v3<S> operator*(float s, v3<S> a) { return mkv<S>(pmul<S>(a.x, s), pmul<S>(a.y, s), pmul<S>(a.z, s)); }
+template <int S> PH_HD v3<S> operator/(v3<S> a, float s) { float inv = 1.0f / s; return a * inv; }
+template <int S> PH_HD float dot(v3<S> a, v3<S> b) { return padd<S>(padd<S>(pmul<S>(a.x, b.x), pmul<S>(a.y, b.y)), pmul<S>(a.z, b.z)); }
+template <int S> PH_HD v3<S> normalize(v3<S> v) { float inv = 1.0f / sqrtf(dot(v, v)); return v * inv; }
+PH_HD float dot_rn(f3 a, f3 b) { return dot(a, b); }
 PH_HD float qnanf() {
 #if defined(__CUDA_ARCH__)
     return __int_as_float(0x7fffffff);
