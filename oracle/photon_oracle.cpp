@@ -16,7 +16,7 @@
  * Parity pin: the reference ships no golden vectors for this path;
  * this restatement is pinned against the reference's own source compiled for the
  * host (oracle/build_ref.sh -> oracle/_ref/libphoton_ref_cpu.so) on recorded inputs,
- * see tests/test_oracle_vs_reference.py and tests/golden/.
+ * see tests/test_golden.py (bit-exact per-ray dumps on 9 scenes) and tests/golden/.
  *
  * Deliberate differences from the reference (all documented in DESIGN.md):
  *  - the image is accumulated in double and rounded to float once (the reference uses

@@ -13,7 +13,7 @@ HEADERS = ["vecmath.cuh", "ray_stages.cuh", "ray_optics.cuh", "trace_core.cuh", 
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared", "--use_fast_math=false",
+    "-Xcompiler", "-fPIC", "-shared", "-fmad=false",     # FMA only where the code asks for it (vecmath.cuh)
 ]
 
 
@@ -36,7 +36,7 @@ def build(force=False, verbose=False):
     if not force and not is_stale():
         return LIB
     os.makedirs(LIBDIR, exist_ok=True)
-    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+    flags = list(NVCC_FLAGS)
     cmd = [nvcc_path()] + flags + (["-Xptxas", "-v"] if verbose else []) + \
           ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lz"]
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -83,11 +83,16 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
     P.mx = mk3((float)xmax, (float)ymax, (float)zmax);
     P.scale = mk3(1.0f / (P.mx.x - P.mn.x), 1.0f / (P.mx.y - P.mn.y), 1.0f / (P.mx.z - P.mn.z));
     P.W = sx; P.H = sy; P.D = sz;
-    P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
+    P.Wf = (float)sx; P.Hf = (float)sy; P.Df = (float)sz; P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
     float step = (float)fmin(dx, dy);
     step = step < dz ? step : (float)dz;
     P.step = step;
     size_t n = (size_t)sx * sy * sz;
+    if (n >= ((size_t)1 << 32)) {        // the sampler indexes voxels with 32 bits (ray_stages.cuh)
+        g_error = "density field has 2^32 voxels or more; not supported by this build";
+        fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
+        return false;
+    }
     float *d_rho = nullptr; unsigned int *d_min = nullptr;
     CK(cudaMalloc(&d_rho, n * sizeof(float)));
     CK(cudaMalloc(&F.lin, n * sizeof(f4)));
@@ -173,6 +178,7 @@ struct photon_scene {
     float last_ms = 0.0f;
     int last_launches = 0, total_launches = 0;
     int grid_blocks = 0;
+    int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
 };
 
 namespace {
@@ -192,14 +198,19 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     a.point_begin = point_begin; a.point_count = point_count; a.dump_point_base = dump_base;
     a.final_pos = fpos; a.final_dir = fdir; a.n_save = n_save;
     a.inter_pos = ipos; a.inter_dir = idir; a.n_inter = n_inter;
+    const bool dump = fpos != nullptr || ipos != nullptr;
     int grid = std::min(point_count, s->grid_blocks);
     if (s->use_texture) {
         TextureField S; S.tex = s->field->tex;
-        trace_rays_kernel<TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        if (dump) trace_rays_kernel<true, 2, TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else trace_rays_kernel<false, 2, TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     } else {
         LinearField S; S.g = s->field ? s->field->lin : nullptr;
         S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
-        trace_rays_kernel<LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (s->occupancy >= 4) trace_rays_kernel<false, 4, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (s->occupancy == 3) trace_rays_kernel<false, 3, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else trace_rays_kernel<false, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     }
     CK(cudaGetLastError());
     s->last_launches++; s->total_launches++;
@@ -302,7 +313,8 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
     // persistent grid: a multiple of the SM count (148 on B200), 2 CTAs resident per SM
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, s->device));
-    int mult = 2 * 4;
+    if (const char *o = getenv("PHOTON_OCC")) s->occupancy = std::max(2, std::min(4, atoi(o)));
+    int mult = s->occupancy * 4;
     if (const char *g = getenv("PHOTON_GRID_MULT")) mult = std::max(1, atoi(g));
     s->grid_blocks = prop.multiProcessorCount * mult;
     CK(cudaStreamSynchronize(s->stream));

@@ -55,7 +55,7 @@ struct SensorSample {
     bool valid;
 };
 
-template <class Sampler>
+template <bool DUMP, class Sampler>
 PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr,
                                                   long long gid, bool save, unsigned long long &steps) {
     SensorSample out; out.valid = false; out.d_x = out.d_y = 0; out.radiance = 0; out.c4 = 0;
@@ -77,17 +77,17 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
         ray.pos = mat_mul(a.cam.inv_rot, rp);
         ray.dir = mat_mul(a.cam.inv_rot, ray.dir);
         IntermediateDump im; im.n = 0; im.pos = nullptr; im.dir = nullptr;
-        if (a.inter_pos && gid < a.n_save) {
+        if (DUMP && a.inter_pos && gid < a.n_save) {
             im.pos = a.inter_pos + (size_t)gid * a.n_inter; im.dir = a.inter_dir + (size_t)gid * a.n_inter; im.n = a.n_inter;
         }
-        steps += (unsigned long long)trace_volume(ray, a.field, S, a.algorithm, im, a.add_ngrad_noise != 0, a.ngrad_noise_std, ns);
+        steps += (unsigned long long)trace_volume<DUMP>(ray, a.field, S, a.algorithm, im, a.add_ngrad_noise != 0, a.ngrad_noise_std, ns);
         rp = mat_mul(a.cam.rot, ray.pos);
         ray.dir = normalize(mat_mul(a.cam.rot, ray.dir));
         rp.z = (float)((double)rp.z + a.z_shift);
         ray.pos = rp;
         if (any_nan(ray.dir) || any_nan(ray.pos)) return out;
     }
-    if (save) a.final_dir[gid] = ray.dir;                                // prt.cu:2136-2141
+    if (DUMP && save) a.final_dir[gid] = ray.dir;                                // prt.cu:2136-2141
     bool flip = true;
     f3 hit;
     if (a.train.e[0].type == 'n') {                                      // prt.cu:1545-1733
@@ -111,7 +111,7 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
     }
     bool on = pixel_coords(hit, a.cam, flip, out.d_x, out.d_y);
     if (!on || is_nan(hit.x) || is_nan(hit.y)) return out;               // dump stays NaN (prt.cu:1449-1455, 2196)
-    if (save) a.final_pos[gid] = hit;
+    if (DUMP && save) a.final_pos[gid] = hit;
     out.radiance = ray.radiance;
     out.c4 = cos4_alpha(ray.dir);
     out.valid = true;

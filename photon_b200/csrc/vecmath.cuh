@@ -14,9 +14,11 @@
 #if defined(__CUDACC__)
 #define PH_HD __host__ __device__ __forceinline__
 #define PH_D __device__ __forceinline__
+#define PH_COLD __host__ __device__ __noinline__     // rare paths kept out of the hot loop's code
 #else
 #define PH_HD inline
 #define PH_D inline
+#define PH_COLD inline
 #endif
 
 namespace ph {
@@ -37,37 +39,50 @@ PH_HD float add_rn(float a, float b) {
 #endif
 }
 
-// Two flavours of the same 3-vector:
-//   f3 = v3<1>  every multiply and add is rounded on its own (no FMA contraction).  Used by the
-//               per-ray stages -- generation, frame rotations, lens, sensor -- whose float32
-//               arithmetic at |coordinates| ~ 1e6 um cancels catastrophically (ray-sphere
-//               quadratic prt.cu:271-276, plane hits), so that a fused multiply-add moves the
-//               sensor hit by more than the 1e-3 px parity tolerance.  The reference's debug
-//               build (-G -O0) does not contract either.
-//   q3 = v3<0>  plain operators that nvcc contracts into FFMA.  Used only inside the integrator
-//               loop (rk4_march / euler_march and the trilinear fetch), where the FP32 issue
-//               rate is the bound and the contraction error is ~1e-7 relative per step.
-template <int STRICT> struct v3 { float x, y, z; };
-typedef v3<1> f3;
-typedef v3<0> q3;
+// f3: every multiply and add is rounded on its own (no FMA contraction), whatever the compiler
+// flags.  The per-ray stages -- generation, frame rotations, lens, sensor -- work in float32 at
+// |coordinates| ~ 1e6 um where sums cancel catastrophically (ray-sphere quadratic
+// prt.cu:271-276, plane hits), and the reference's debug build (-G -O0) does not contract.
+// The library is also compiled with -fmad=false so that the scalar expressions of those
+// stages stay unfused; the integrator loop asks for its fused multiply-adds explicitly
+// through ph::fma_ (below), which is the only place where FMA is wanted.
+struct f3 { float x, y, z; };
 struct f4 { float x, y, z, w; };
 
-template <int S> PH_HD float pmul(float a, float b) { return S ? mul_rn(a, b) : a * b; }
-template <int S> PH_HD float padd(float a, float b) { return S ? add_rn(a, b) : a + b; }
-
-template <int S> PH_HD v3<S> mkv(float x, float y, float z) { v3<S> r; r.x = x; r.y = y; r.z = z; return r; }
-PH_HD f3 mk3(float x, float y, float z) { return mkv<1>(x, y, z); }
-PH_HD q3 relax(f3 a) { return mkv<0>(a.x, a.y, a.z); }
-PH_HD f3 strict(q3 a) { return mkv<1>(a.x, a.y, a.z); }
-template <int S> PH_HD v3<S> operator+(v3<S> a, v3<S> b) { return mkv<S>(padd<S>(a.x, b.x), padd<S>(a.y, b.y), padd<S>(a.z, b.z)); }
-template <int S> PH_HD v3<S> operator-(v3<S> a, v3<S> b) { return mkv<S>(padd<S>(a.x, -b.x), padd<S>(a.y, -b.y), padd<S>(a.z, -b.z)); }
-template <int S> PH_HD v3<S> operator-(v3<S> a) { return mkv<S>(-a.x, -a.y, -a.z); }
-template <int S> PH_HD v3<S> operator*(v3<S> a, float s) { return mkv<S>(pmul<S>(a.x, s), pmul<S>(a.y, s), pmul<S>(a.z, s)); }
-template <int S> PH_HD v3<S> operator*(float s, v3<S> a) { return mkv<S>(pmul<S>(a.x, s), pmul<S>(a.y, s), pmul<S>(a.z, s)); }
-template <int S> PH_HD v3<S> operator/(v3<S> a, float s) { float inv = 1.0f / s; return a * inv; }
-template <int S> PH_HD float dot(v3<S> a, v3<S> b) { return padd<S>(padd<S>(pmul<S>(a.x, b.x), pmul<S>(a.y, b.y)), pmul<S>(a.z, b.z)); }
-template <int S> PH_HD v3<S> normalize(v3<S> v) { float inv = 1.0f / sqrtf(dot(v, v)); return v * inv; }
+PH_HD f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+PH_HD f3 operator+(f3 a, f3 b) { return mk3(add_rn(a.x, b.x), add_rn(a.y, b.y), add_rn(a.z, b.z)); }
+PH_HD f3 operator-(f3 a, f3 b) { return mk3(add_rn(a.x, -b.x), add_rn(a.y, -b.y), add_rn(a.z, -b.z)); }
+PH_HD f3 operator-(f3 a) { return mk3(-a.x, -a.y, -a.z); }
+PH_HD f3 operator*(f3 a, float s) { return mk3(mul_rn(a.x, s), mul_rn(a.y, s), mul_rn(a.z, s)); }
+PH_HD f3 operator*(float s, f3 a) { return mk3(mul_rn(a.x, s), mul_rn(a.y, s), mul_rn(a.z, s)); }
+PH_HD f3 operator/(f3 a, float s) { float inv = 1.0f / s; return a * inv; }
+PH_HD float dot(f3 a, f3 b) { return add_rn(add_rn(mul_rn(a.x, b.x), mul_rn(a.y, b.y)), mul_rn(a.z, b.z)); }
+PH_HD f3 normalize(f3 v) { float inv = 1.0f / sqrtf(dot(v, v)); return v * inv; }
 PH_HD float dot_rn(f3 a, f3 b) { return dot(a, b); }
+
+// Integrator-loop arithmetic.  fma_(a,b,c) = a*b+c: one FFMA on the GPU.  With PH_NO_FMA
+// (tests/hostcheck) it is the unfused product and sum, which reproduces the reference's
+// operation order bit for bit on the CPU; the fused form differs by <= 1/2 ulp per operation.
+PH_HD float fma_(float a, float b, float c) {
+#if defined(PH_NO_FMA)
+    return add_rn(mul_rn(a, b), c);
+#else
+    return fmaf(a, b, c);
+#endif
+}
+PH_HD f3 axpy(float s, f3 v, f3 w) { return mk3(fma_(s, v.x, w.x), fma_(s, v.y, w.y), fma_(s, v.z, w.z)); }   // s*v + w
+PH_HD f3 scale3(float s, f3 v) { return mk3(s * v.x, s * v.y, s * v.z); }
+// floor(x) as float plus the integer, for |x| < 2^22, without the conversion pipe: adding
+// 1.5*2^23 with round-down leaves floor(x) in the low mantissa bits (FADD.RM + FADD + IADD).
+PH_HD float floor_split(float x, int &i) {
+#if defined(__CUDA_ARCH__)
+    float t = __fadd_rd(x, 12582912.0f);
+    i = __float_as_int(t) - 0x4B400000;
+    return __fadd_rn(t, -12582912.0f);
+#else
+    float f = floorf(x); i = (int)f; return f;
+#endif
+}
 PH_HD float qnanf() {
 #if defined(__CUDA_ARCH__)
     return __int_as_float(0x7fffffff);

@@ -30,7 +30,7 @@ def hostcheck_lib():
     newest = max(newest, os.path.getmtime(src))
     if not os.path.exists(out) or os.path.getmtime(out) < newest:
         gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-        subprocess.run([gxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-o", out, src, "-lz"], check=True)
+        subprocess.run([gxx, "-O2", "-std=c++17", "-DPH_NO_FMA", "-ffp-contract=off", "-fPIC", "-shared", "-x", "c++", "-o", out, src, "-lz"], check=True)
     return ctypes.CDLL(out)
 
 

@@ -57,7 +57,7 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
         FieldParams P{};
         P.mn = mk3((float)xmin, (float)ymin, (float)zmin); P.mx = mk3((float)xmax, (float)ymax, (float)zmax);
         P.scale = mk3(1.0f / (P.mx.x - P.mn.x), 1.0f / (P.mx.y - P.mn.y), 1.0f / (P.mx.z - P.mn.z));
-        P.W = sx; P.H = sy; P.D = sz; P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
+        P.W = sx; P.H = sy; P.D = sz; P.Wf = (float)sx; P.Hf = (float)sy; P.Df = (float)sz; P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
         float step = (float)fmin(dx, dy); step = step < dz ? step : (float)dz; P.step = step;
         field.resize((size_t)sx * sy * sz);
         float dmin = INFINITY;
@@ -91,7 +91,7 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
             for (int lr = 0; lr < rpp; lr++) {
                 long long gid = (long long)lr + (long long)(p - begin) * rpp;
                 bool save = dumps && gid < num_lightrays_save;
-                SensorSample s = trace_one(a, S, p, lr, gid, save, steps);
+                SensorSample s = trace_one<true>(a, S, p, lr, gid, save, steps);
                 if (!s.valid) continue;
                 if (erf_model) {
                     ErfFootprint fp; erf_footprint(fp, s.d_x, s.d_y, s.radiance, s.c4, a.cam.diffraction_diameter, erf_frac);

@@ -26,3 +26,33 @@ def test_stage_code_bit_exact_vs_oracle(name, cases, hostcheck_lib, oracle_lib, 
     assert np.array_equal(ref[2], got[2], equal_nan=True)
     m = util.compare(ref, got, pitch)
     assert m["image_rel_l2"] <= 1e-7, m
+
+
+def test_thick_lens_conditioning(cases, oracle_lib, tmp_path):
+    """Measures how far a ONE-ulp change of the generated tangents (what a different libm does to
+    prt.cu:128-130,228) moves the sensor hits in the reference's float32 arithmetic.  This is the
+    justification for tests/util.THICK_LENS_MAX_PX: thick-lens scenes cannot be reproduced to
+    1e-3 px on every ray by ANY implementation whose tanf/atanf differ in the last bit."""
+    import ctypes
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = os.path.join(root, "tests", "hostcheck", "hostcheck.cpp")
+    out = str(tmp_path / "libhostcheck_perturbed.so")
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    subprocess.run([gxx, "-O2", "-std=c++17", "-DPH_NO_FMA", "-DPH_PERTURB_GEN", "-ffp-contract=off", "-fPIC", "-shared",
+                    "-x", "c++", "-o", out, src, "-lz"], check=True, capture_output=True)
+    pert = ctypes.CDLL(out)
+    res = {}
+    for name in ("piv_mie_thick_bilinear", "piv_diffuse_thin_bilinear", "bos_rk4_thin_diffraction"):
+        call, pitch = cases[name]
+        d0 = tmp_path / (name + "_o"); d0.mkdir()
+        d1 = tmp_path / (name + "_p"); d1.mkdir()
+        ref = util.run_with_dumps(oracle_lib, call, str(d0))
+        got = util.run_with_dumps(pert, call, str(d1))
+        res[name] = util.compare(ref, got, pitch)
+    print({k: (v["dpos_px"], v["dpos_px_p999"]) for k, v in res.items()})
+    assert res["piv_diffuse_thin_bilinear"]["dpos_px"] <= util.TOL_POS_PX       # thin lens / BOS: well conditioned
+    assert res["bos_rk4_thin_diffraction"]["dpos_px"] <= util.TOL_POS_PX
+    thick = res["piv_mie_thick_bilinear"]
+    assert thick["dpos_px_p999"] <= util.TOL_POS_PX and thick["dpos_px"] <= util.THICK_LENS_MAX_PX
