@@ -108,20 +108,36 @@ def cpu_reference_lib():
 
 
 def time_cpu(call, npoints, lib, kind):
-    """Trace the first npoints source points of the workload on the host cores."""
+    """Trace the first npoints source points of the workload on the host cores.
+    kind "port": the oracle restatement (counts committed steps itself).
+    kind "reference": the reference's own sources compiled for the host (oracle/_ref); its kernel time
+    is the time inside its parallel_ray_tracing launches and its ray-steps are tex3D fetches // 3
+    (RK4 samples the field 3 times per committed step; the one discarded step per ray adds < 0.3 %)."""
+    import ctypes
     sub = call.subset(slice(0, npoints))
-    t0 = time.perf_counter()
-    sub.run(lib)
-    wall = time.perf_counter() - t0
+    if kind == "reference":
+        lib.photon_ref_last_trace_seconds.restype = ctypes.c_double
+        lib.photon_ref_last_tex_fetches.restype = ctypes.c_longlong
+        lib.photon_ref_reset_counters()
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(1)
+    sys.stdout.flush()
+    os.dup2(devnull, 1)                       # the reference prints progress lines on stdout
+    try:
+        t0 = time.perf_counter()
+        sub.run(lib)
+        wall = time.perf_counter() - t0
+    finally:
+        os.dup2(saved, 1)
+        os.close(devnull)
+        os.close(saved)
     if kind == "port":
         secs = lib.photon_oracle_last_trace_seconds()
         steps = lib.photon_oracle_last_ray_steps()
         threads = lib.photon_oracle_last_threads()
     else:
-        lib.photon_ref_last_trace_seconds.restype = __import__("ctypes").c_double
-        lib.photon_ref_last_ray_steps.restype = __import__("ctypes").c_longlong
         secs = lib.photon_ref_last_trace_seconds()
-        steps = lib.photon_ref_last_ray_steps()
+        steps = lib.photon_ref_last_tex_fetches() // 3
         threads = lib.photon_ref_last_threads()
     return {"seconds": secs, "wall": wall, "steps": int(steps), "rays": int(npoints * call.lightray_number_per_particle),
             "threads": int(threads)}
@@ -135,8 +151,8 @@ def run_reference_arm(args):
     workdir = args.workdir or tempfile.mkdtemp(prefix="photon_bench_")
     call, _ = build_workload(args, workdir, 0)
     lib, kind = cpu_reference_lib()
-    pilot = time_cpu(call, 8, lib, kind)          # loads the field, sizes the per-step sample (~10 s of CPU work)
-    npts = args.cpu_sample_points or int(max(8, min(2000, 10.0 * 8 / max(pilot["seconds"], 1e-3))))
+    pilot = time_cpu(call, 16, lib, kind)         # sizes the per-step sample: about 6 s of tracing per step
+    npts = args.cpu_sample_points or int(max(16, min(2000, 6.0 * 16 / max(pilot["seconds"], 1e-3))))
     for _ in range(args.warmup):
         time_cpu(call, 8, lib, kind)
     secs, steps, rays, threads = 0.0, 0, 0, 1
@@ -152,7 +168,8 @@ def run_reference_arm(args):
             "config": workload_config(args, call),
             "cpu_baseline": {"value": v, "unit": "ray-steps/s", "cores": threads, "kind": kind,
                              "sample": f"{npts} source points x {args.rays_per_point} rays per step ({rays} rays total), "
-                                       "field load excluded"},
+                                       "time inside the tracing kernel launches; the per-call NRRD load + gradient precompute "
+                                       "(about 10 s at 512^3, single-threaded in the reference) is excluded"},
             "e2e": {"value": v, "unit": "ray-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -306,8 +323,8 @@ def main():
         }
         if not args.no_cpu_baseline and world == 1:
             cl, kind = cpu_reference_lib()
-            pilot = time_cpu(call, 8, cl, kind)     # also loads the field once (excluded from the timing anyway)
-            n = args.cpu_sample_points or int(max(8, min(4000, 15.0 * 8 / max(pilot["seconds"], 1e-3))))
+            pilot = time_cpu(call, 16, cl, kind)    # sizes the sample: about 12 s of tracing on the host cores
+            n = args.cpu_sample_points or int(max(16, min(4000, 12.0 * 16 / max(pilot["seconds"], 1e-3))))
             r = time_cpu(call, n, cl, kind)
             line["cpu_baseline"] = {"value": r["steps"] / r["seconds"], "unit": "ray-steps/s", "cores": r["threads"],
                                     "kind": kind, "rays_per_s": r["rays"] / r["seconds"],

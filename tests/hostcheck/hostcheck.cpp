@@ -57,7 +57,10 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
         FieldParams P{};
         P.mn = mk3((float)xmin, (float)ymin, (float)zmin); P.mx = mk3((float)xmax, (float)ymax, (float)zmax);
         P.scale = mk3(1.0f / (P.mx.x - P.mn.x), 1.0f / (P.mx.y - P.mn.y), 1.0f / (P.mx.z - P.mn.z));
-        P.W = sx; P.H = sy; P.D = sz; P.Wf = (float)sx; P.Hf = (float)sy; P.Df = (float)sz; P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
+        P.W = sx; P.H = sy; P.D = sz; P.Wf = (float)sx; P.Hf = (float)sy; P.Df = (float)sz;
+        { double k[3] = {(double)P.scale.x * (sx - 2), (double)P.scale.y * (sy - 2), (double)P.scale.z * (sz - 2)};
+          P.tk = mk3((float)k[0], (float)k[1], (float)k[2]);
+          P.tc = mk3((float)(0.5 - (double)P.mn.x * k[0]), (float)(0.5 - (double)P.mn.y * k[1]), (float)(0.5 - (double)P.mn.z * k[2])); } P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
         float step = (float)fmin(dx, dy); step = step < dz ? step : (float)dz; P.step = step;
         field.resize((size_t)sx * sy * sz);
         float dmin = INFINITY;
