@@ -99,6 +99,8 @@ int photon_b200_load_field(const char *path, float meta16[16], float *out_float4
 /* FP32 FMA throughput of the device in TFLOP/s, measured with a register-resident FFMA loop
  * (the roofline denominator for the trace kernel, which is FP32-issue bound, not HBM bound). */
 double photon_b200_measure_fp32_tflops(int device);
+/* The same loop with Blackwell's packed FFMA2 (two FP32 FMAs per issued instruction). */
+double photon_b200_measure_fp32x2_tflops(int device);
 
 #ifdef __cplusplus
 }

@@ -31,20 +31,22 @@ def is_stale():
     return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
 
 
-def build(force=False, verbose=False):
-    """Compile the CUDA library if it is missing or older than its sources."""
-    if not force and not is_stale():
+def build(force=False, verbose=False, defines=(), out=None):
+    """Compile the CUDA library if it is missing or older than its sources.  ``defines``/``out`` build
+    an experimental variant beside it (tools/gpu_sweep.sh selects one with PHOTON_B200_LIB)."""
+    if not force and not is_stale() and out is None:
         return LIB
     os.makedirs(LIBDIR, exist_ok=True)
-    flags = list(NVCC_FLAGS)
+    flags = list(NVCC_FLAGS) + ["-D" + d for d in defines]
+    out = out or LIB
     cmd = [nvcc_path()] + flags + (["-Xptxas", "-v"] if verbose else []) + \
-          ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lz"]
+          ["-o", out] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lz"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stderr)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":

@@ -630,9 +630,28 @@ __global__ void __launch_bounds__(256) fp32_peak_kernel(float *out, int iters, f
     float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
     if (s == 123.456f) out[0] = s;
 }
+// the same with Blackwell's packed FFMA2 (fma.rn.f32x2): two FP32 FMAs per issued instruction
+__global__ void __launch_bounds__(256) fp32x2_peak_kernel(float *out, int iters, float a, float b) {
+    float t = threadIdx.x * 1e-3f;
+    float2 x0 = make_float2(t, t + 1), x1 = make_float2(t + 2, t + 3), x2 = make_float2(t + 4, t + 5), x3 = make_float2(t + 6, t + 7);
+    float2 x4 = make_float2(t + 8, t + 9), x5 = make_float2(t + 10, t + 11), x6 = make_float2(t + 12, t + 13), x7 = make_float2(t + 14, t + 15);
+    const float2 aa = make_float2(a, a), bb = make_float2(b, b);
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            x0 = __ffma2_rn(x0, aa, bb); x1 = __ffma2_rn(x1, aa, bb); x2 = __ffma2_rn(x2, aa, bb); x3 = __ffma2_rn(x3, aa, bb);
+            x4 = __ffma2_rn(x4, aa, bb); x5 = __ffma2_rn(x5, aa, bb); x6 = __ffma2_rn(x6, aa, bb); x7 = __ffma2_rn(x7, aa, bb);
+        }
+    }
+    float s = x0.x + x1.x + x2.x + x3.x + x4.x + x5.x + x6.x + x7.x + x0.y + x1.y + x2.y + x3.y + x4.y + x5.y + x6.y + x7.y;
+    if (s == 123.456f) out[0] = s;
+}
 }  // namespace
 
-extern "C" double photon_b200_measure_fp32_tflops(int device) {
+static double measure_fp32(int device, bool packed);
+extern "C" double photon_b200_measure_fp32_tflops(int device) { return measure_fp32(device, false); }
+extern "C" double photon_b200_measure_fp32x2_tflops(int device) { return measure_fp32(device, true); }
+static double measure_fp32(int device, bool packed) {
     if (photon_b200_device_count() < 1) return -1.0;
     int dev = pick_device(device);
     if (cudaSetDevice(dev) != cudaSuccess) return -1.0;
@@ -645,11 +664,12 @@ extern "C" double photon_b200_measure_fp32_tflops(int device) {
     double best = 0.0;
     for (int rep = 0; rep < 5; rep++) {
         cudaEventRecord(e0);
-        fp32_peak_kernel<<<blocks, threads>>>(d, iters, 0.999f, 0.001f);
+        if (packed) fp32x2_peak_kernel<<<blocks, threads>>>(d, iters, 0.999f, 0.001f);
+        else fp32_peak_kernel<<<blocks, threads>>>(d, iters, 0.999f, 0.001f);
         cudaEventRecord(e1);
         if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
         float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
-        double flops = 2.0 * 8 * 16 * (double)iters * threads * blocks;
+        double flops = (packed ? 2.0 : 1.0) * 2.0 * 8 * 16 * (double)iters * threads * blocks;
         double tf = flops / (ms * 1e-3) / 1e12;
         if (rep > 0 && tf > best) best = tf;
     }

@@ -14,7 +14,7 @@ class PhotonLibraryError(RuntimeError):
 
 
 def library_path():
-    return _build.LIB
+    return os.environ.get("PHOTON_B200_LIB") or _build.LIB
 
 
 def load_library(require_gpu=False):
@@ -60,6 +60,8 @@ def load_library(require_gpu=False):
         lib.photon_scene_trace_range.restype = C.c_int
         lib.photon_b200_measure_fp32_tflops.argtypes = [C.c_int]
         lib.photon_b200_measure_fp32_tflops.restype = C.c_double
+        lib.photon_b200_measure_fp32x2_tflops.argtypes = [C.c_int]
+        lib.photon_b200_measure_fp32x2_tflops.restype = C.c_double
         _lib = lib
     if require_gpu and _lib.photon_b200_device_count() < 1:
         raise PhotonLibraryError("no CUDA device visible; photon_b200 has no CPU fallback")
