@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <sys/stat.h>
+#include <chrono>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -148,11 +149,50 @@ DeviceField *get_field(const char *path, int device, cudaStream_t st) {
     return slot;
 }
 
+// Per-call buffers come from the device's stream-ordered memory pool, which is told to keep what is
+// freed (release threshold = max): after the first call a scene costs no cudaMalloc/cudaFree.
+void keep_pool_memory(int device) {
+    static std::mutex m; static std::vector<int> done;
+    std::lock_guard<std::mutex> lk(m);
+    for (int d : done) if (d == device) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    cudaGetLastError();
+    done.push_back(device);
+}
+template <class T>
+bool pool_alloc(T *&dst, size_t bytes, cudaStream_t st) {
+    dst = nullptr;
+    CK(cudaMallocAsync((void **)&dst, bytes ? bytes : 1, st));
+    return true;
+}
+template <class T>
+void pool_free(T *p, cudaStream_t st) { if (p) cudaFreeAsync((void *)p, st); }
+
+// Pinned staging for the image copies (one buffer per host thread, grown on demand).
+struct PinnedStage {
+    void *p = nullptr; size_t cap = 0;
+    void *get(size_t bytes) {
+        if (bytes > cap) {
+            if (p) cudaFreeHost(p);
+            p = nullptr; cap = 0;
+            if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); p = nullptr; return nullptr; }
+            cap = bytes;
+        }
+        return p;
+    }
+    ~PinnedStage() { if (p) cudaFreeHost(p); }
+};
+thread_local PinnedStage g_stage;
+
 template <class T>
 bool upload(T *&dst, const T *src, size_t n, cudaStream_t st) {
     dst = nullptr;
     if (n == 0) return true;
-    CK(cudaMalloc(&dst, n * sizeof(T)));
+    if (!pool_alloc(dst, n * sizeof(T), st)) return false;
     CK(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
     return true;
 }
@@ -247,6 +287,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
                        int algorithm, bool add_pos_noise, float pos_noise_std, bool add_ngrad_noise,
                        float ngrad_noise_std, float cone_ratio, int shard_index, int shard_count) {
     CK(cudaSetDevice(s->device));
+    keep_pool_memory(s->device);
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
@@ -307,19 +348,19 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
     }
 
     // ---- image + counters
-    CK(cudaMalloc(&s->d_image, (size_t)c.nx * c.ny * sizeof(float)));
+    if (!pool_alloc(s->d_image, (size_t)c.nx * c.ny * sizeof(float), s->stream)) return false;
     CK(cudaMemsetAsync(s->d_image, 0, (size_t)c.nx * c.ny * sizeof(float), s->stream));
-    CK(cudaMalloc(&s->d_counters, 2 * sizeof(unsigned long long)));
+    if (!pool_alloc(s->d_counters, 2 * sizeof(unsigned long long), s->stream)) return false;
     CK(cudaMemsetAsync(s->d_counters, 0, 2 * sizeof(unsigned long long), s->stream));
     a.image = s->d_image; a.counters = s->d_counters;
 
     // persistent grid: a multiple of the SM count (148 on B200), 2 CTAs resident per SM
-    cudaDeviceProp prop;
-    CK(cudaGetDeviceProperties(&prop, s->device));
+    int sm_count = 148;
+    CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device));
     if (const char *o = getenv("PHOTON_OCC")) s->occupancy = std::max(2, std::min(4, atoi(o)));
     int mult = s->occupancy * 4;
     if (const char *g = getenv("PHOTON_GRID_MULT")) mult = std::max(1, atoi(g));
-    s->grid_blocks = prop.multiProcessorCount * mult;
+    s->grid_blocks = sm_count * mult;
     CK(cudaStreamSynchronize(s->stream));
     return true;
 }
@@ -356,8 +397,10 @@ void photon_scene_destroy(photon_scene *s) {
     if (!s) return;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
-    cudaFree(s->d_sx); cudaFree(s->d_sy); cudaFree(s->d_sz); cudaFree(s->d_srad); cudaFree(s->d_sdiam);
-    cudaFree(s->d_angle); cudaFree(s->d_irr); cudaFree(s->d_aim); cudaFree(s->d_image); cudaFree(s->d_counters);
+    cudaStream_t st = s->stream;
+    pool_free(s->d_sx, st); pool_free(s->d_sy, st); pool_free(s->d_sz, st); pool_free(s->d_srad, st); pool_free(s->d_sdiam, st);
+    pool_free(s->d_angle, st); pool_free(s->d_irr, st); pool_free(s->d_aim, st); pool_free(s->d_image, st); pool_free(s->d_counters, st);
+    if (st) cudaStreamSynchronize(st);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -373,14 +416,22 @@ int photon_scene_zero_image(photon_scene *s) {
 }
 int photon_scene_upload_image(photon_scene *s, const float *h) {
     if (!scene_ok(s)) return 1;
-    return cuda_ok(cudaMemcpyAsync(s->d_image, h, (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float),
-                                   cudaMemcpyHostToDevice, s->stream), "image H2D", __FILE__, __LINE__) ? 0 : 1;
+    const size_t bytes = (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float);
+    const void *src = h;
+    if (void *stage = g_stage.get(bytes)) {           // pinned staging; the copy below is then truly asynchronous
+        if (!cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__)) return 1;   // staging buffer is reused
+        memcpy(stage, h, bytes); src = stage;
+    }
+    return cuda_ok(cudaMemcpyAsync(s->d_image, src, bytes, cudaMemcpyHostToDevice, s->stream), "image H2D", __FILE__, __LINE__) ? 0 : 1;
 }
 int photon_scene_download_image(photon_scene *s, float *h) {
     if (!scene_ok(s)) return 1;
-    if (!cuda_ok(cudaMemcpyAsync(h, s->d_image, (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float),
-                                 cudaMemcpyDeviceToHost, s->stream), "image D2H", __FILE__, __LINE__)) return 1;
-    return cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__) ? 0 : 1;
+    const size_t bytes = (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float);
+    void *stage = g_stage.get(bytes);
+    if (!cuda_ok(cudaMemcpyAsync(stage ? stage : (void *)h, s->d_image, bytes, cudaMemcpyDeviceToHost, s->stream), "image D2H", __FILE__, __LINE__)) return 1;
+    if (!cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__)) return 1;
+    if (stage) memcpy(h, stage, bytes);
+    return 0;
 }
 void *photon_scene_image_device_ptr(photon_scene *s) { return s ? (void *)s->d_image : nullptr; }
 
@@ -554,10 +605,20 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
                                    si, sc, dev);
     };
 
+    const bool timing = getenv("PHOTON_TIMING") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[photon timing] %-16s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     if (ngpus == 1) {
         photon_scene *s = make_scene(shard_index, shard_count, -1);
         if (!s) return;                                                  // image untouched
+        lap("scene create");
         bool ok = photon_scene_upload_image(s, image_array) == 0;        // accumulate onto the caller's image (prt.cu:3309)
+        lap("image H2D");
         if (ok && (dumps || inter)) {
             int spn = std::min(lightfield_source_p->source_point_number, np);
             int kmax = spn > 0 ? (np + spn - 1) / spn : 0;               // prt.cu:3506-3510
@@ -581,12 +642,14 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
         } else if (ok) {
             ok = photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
         }
+        lap("trace");
         if (ok) {
-            std::vector<float> tmp(npix);
-            if (photon_scene_download_image(s, tmp.data()) == 0) memcpy(image_array, tmp.data(), npix * sizeof(float));
+            photon_scene_download_image(s, image_array);         // through pinned staging: all or nothing
+            lap("image D2H");
             VLOG("traced %lld rays, %lld ray-steps, kernel %.3f ms\n", photon_scene_rays(s), photon_scene_ray_steps(s), photon_scene_last_trace_ms(s));
         }
         photon_scene_destroy(s);
+        lap("scene destroy");
         return;
     }
 
