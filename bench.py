@@ -101,6 +101,9 @@ class ClockSampler:
 def cpu_reference_lib():
     """(lib, kind): the reference's own source compiled for the host if present, else the oracle port."""
     from oracle.loader import load_oracle, load_ref_cpu
+    # all host cores (torchrun exports OMP_NUM_THREADS=1 to its workers; the OpenMP runtime reads the
+    # variable when the library is loaded)
+    os.environ["OMP_NUM_THREADS"] = os.environ.get("PHOTON_BENCH_THREADS") or str(os.cpu_count() or 1)
     ref = load_ref_cpu()
     if ref is not None and not os.environ.get("PHOTON_BENCH_FORCE_PORT"):
         return ref, "reference"
