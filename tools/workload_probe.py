@@ -1,0 +1,42 @@
+"""Resident-scene throughput of the non-C3 workloads (rays/s, CUDA-event time).
+usage: python tools/workload_probe.py [piv|piv_diffraction|bos_euler|bos_nograd ...]"""
+import os, sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from photon_b200 import scenes
+from photon_b200.scene import ResidentScene
+
+def make(name, d):
+    if name.startswith("piv"):
+        c = scenes.c1_piv(particles=20000, rays_per_particle=10000)
+        if name == "piv_diffraction":
+            c.camera.implement_diffraction = True; c.camera.diffraction_diameter = 3.0
+        if name == "piv_thin":
+            c = scenes.c1_piv(particles=20000, rays_per_particle=10000, lens_model="thin-lens")
+        if name == "piv_diffuse":
+            c = scenes.c1_piv(particles=20000, rays_per_particle=10000, mie=False)
+        return c
+    nrrd = os.path.join(d, "probe_blob_256.nrrd")
+    alg = 1 if name == "bos_euler" else 2
+    c = scenes.c3_bos(nrrd, n=256, dots_per_side=100, points_per_dot=100, rays_per_point=500, algorithm=alg,
+                      write_field=not os.path.exists(nrrd))
+    if name == "bos_nograd":
+        c.simulate_density_gradients = False
+    return c
+
+d = "/tmp/photon_bench"; os.makedirs(d, exist_ok=True)
+for name in (sys.argv[1:] or ["piv", "piv_thin", "piv_diffuse", "piv_diffraction", "bos_nograd", "bos_euler"]):
+    call = make(name, d)
+    s = ResidentScene(call)
+    n = min(s.num_points, 10000)
+    for k in range(2):
+        s.trace_range(0, n)
+    s.reset_counters(); s.zero_image()
+    ms = []
+    for k in range(3):
+        s.trace_range(0, n); ms.append(s.last_trace_ms)
+    rays = n * call.lightray_number_per_particle
+    img = s.download_image()
+    print("%-16s %8.2f ms  %.3e rays/s  steps/ray %.1f  hits %.3f  image sum %.4g" % (
+        name, np.mean(ms), rays / (np.mean(ms) * 1e-3), s.ray_steps / max(s.rays, 1), s.sensor_hits / max(s.rays, 1), img.sum()), flush=True)
+    s.close()
