@@ -21,6 +21,10 @@
  *   PHOTON_SAMPLER=texture  hardware tex3D<float4> (the reference's 9-bit filter weights)
  *   PHOTON_SHARD=r/n        trace only the r-th of n contiguous source-point shards
  *   PHOTON_GPUS=<n>         split the source points over n GPUs inside one call
+ *   PHOTON_DETERMINISTIC=1  accumulate the image in 64-bit fixed point with integer atomics: the
+ *                           result is bit-identical from run to run and for any sharding
+ *   PHOTON_OCC=<2|3|4>      resident CTAs per SM the trace kernel variant is compiled for
+ *   PHOTON_TIMING=1         per-stage wall times of start_ray_tracing on stderr
  */
 #ifndef PHOTON_B200_H_
 #define PHOTON_B200_H_
@@ -63,6 +67,10 @@ int   photon_scene_zero_image(photon_scene *s);
 int   photon_scene_upload_image(photon_scene *s, const float *host_image);      /* H2D */
 int   photon_scene_download_image(photon_scene *s, float *host_image);          /* D2H, overwrites */
 void *photon_scene_image_device_ptr(photon_scene *s);                           /* for NCCL reduce by the caller */
+/* Deterministic mode: 1 if the scene accumulates in fixed point; the raw int64 image (increments in
+ * units of 1/scale, the same scale for every shard of a call) for an exact cross-GPU sum. */
+int   photon_scene_deterministic(photon_scene *s);
+int   photon_scene_download_image_fixed(photon_scene *s, long long *host_fixed, double *scale);
 
 /*
  * Trace all source points of the scene's shard onto the device image (replaces the

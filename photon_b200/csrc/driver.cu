@@ -215,6 +215,8 @@ struct photon_scene {
     float *d_angle = nullptr, *d_irr = nullptr;
     f2 *d_aim = nullptr;
     float *d_image = nullptr;
+    unsigned long long *d_fixed = nullptr;   // deterministic mode (PHOTON_DETERMINISTIC=1)
+    double fixed_scale = 0.0;
     unsigned long long *d_counters = nullptr;
     unsigned long long h_counters[2] = {0, 0};
     long long rays_traced = 0;
@@ -243,6 +245,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     a.inter_pos = ipos; a.inter_dir = idir; a.n_inter = n_inter;
     const bool dump = fpos != nullptr || ipos != nullptr;
     int grid = std::min(point_count, s->grid_blocks);
+    if (s->use_texture && s->d_fixed) { g_error = "PHOTON_DETERMINISTIC is not available with PHOTON_SAMPLER=texture"; return false; }
     if (s->use_texture) {
         TextureField S; S.tex = s->field->tex;
         if (dump) trace_rays_kernel<true, 2, TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
@@ -250,7 +253,9 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     } else {
         LinearField S; S.g = s->field ? s->field->lin : nullptr;
         S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
-        if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        if (s->d_fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (s->d_fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->occupancy >= 4) trace_rays_kernel<false, 4, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->occupancy == 3) trace_rays_kernel<false, 3, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
@@ -351,6 +356,28 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
     if (!pool_alloc(s->d_image, (size_t)c.nx * c.ny * sizeof(float), s->stream)) return false;
     CK(cudaMemsetAsync(s->d_image, 0, (size_t)c.nx * c.ny * sizeof(float), s->stream));
     if (!pool_alloc(s->d_counters, 2 * sizeof(unsigned long long), s->stream)) return false;
+    if (getenv("PHOTON_DETERMINISTIC") && atoi(getenv("PHOTON_DETERMINISTIC")) != 0) {
+        // Upper bound of the radiance one ray can deposit in one pixel, times ALL rays of the call
+        // (not of the shard: every shard must use the same scale), must stay below 2^62.
+        double rmax = 0.0;
+        for (int i = 0; i < np; i++) { double r = fabs(src->radiance[i]); if (r > rmax) rmax = r; }
+        if (a.mie.enabled) {
+            double imax = 0.0;
+            size_t nt = (size_t)sc->num_angles * sc->num_diameters;
+            for (size_t i = 0; i < nt; i++) { double v = fabs((double)sc->scattering_irradiance[i]); if (v > imax) imax = v; }
+            rmax *= imax;
+        }
+        double tr = 1.0;
+        for (int k = 0; k < ne; k++) tr *= fmax(1.0, fabs((double)element_data[k].element_properties.transmission_ratio));
+        double bound = rmax * (double)a.inv_fnum2 * tr * (double)np * (double)rpp;
+        int e = 0;
+        if (bound > 0 && std::isfinite(bound)) frexp(bound, &e);
+        s->fixed_scale = ldexp(1.0, 62 - e - 1);
+        size_t nb = (size_t)c.nx * c.ny * sizeof(unsigned long long);
+        if (!pool_alloc(s->d_fixed, nb, s->stream)) return false;
+        CK(cudaMemsetAsync(s->d_fixed, 0, nb, s->stream));
+    }
+    a.image_fixed = s->d_fixed; a.fixed_scale = s->fixed_scale;
     CK(cudaMemsetAsync(s->d_counters, 0, 2 * sizeof(unsigned long long), s->stream));
     a.image = s->d_image; a.counters = s->d_counters;
 
@@ -400,6 +427,7 @@ void photon_scene_destroy(photon_scene *s) {
     cudaStream_t st = s->stream;
     pool_free(s->d_sx, st); pool_free(s->d_sy, st); pool_free(s->d_sz, st); pool_free(s->d_srad, st); pool_free(s->d_sdiam, st);
     pool_free(s->d_angle, st); pool_free(s->d_irr, st); pool_free(s->d_aim, st); pool_free(s->d_image, st); pool_free(s->d_counters, st);
+    pool_free(s->d_fixed, st);
     if (st) cudaStreamSynchronize(st);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -411,6 +439,7 @@ static bool scene_ok(photon_scene *s) { if (!s) { g_error = "null scene"; return
 
 int photon_scene_zero_image(photon_scene *s) {
     if (!scene_ok(s)) return 1;
+    if (s->d_fixed) cudaMemsetAsync(s->d_fixed, 0, (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(unsigned long long), s->stream);
     return cuda_ok(cudaMemsetAsync(s->d_image, 0, (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float), s->stream),
                    "zero image", __FILE__, __LINE__) ? 0 : 1;
 }
@@ -424,8 +453,24 @@ int photon_scene_upload_image(photon_scene *s, const float *h) {
     }
     return cuda_ok(cudaMemcpyAsync(s->d_image, src, bytes, cudaMemcpyHostToDevice, s->stream), "image H2D", __FILE__, __LINE__) ? 0 : 1;
 }
+static bool fold_fixed(photon_scene *s) {
+    if (!s->d_fixed) return true;
+    size_t n = (size_t)s->args.cam.nx * s->args.cam.ny;
+    fold_fixed_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 8), 256, 0, s->stream>>>(s->d_image, s->d_fixed, 1.0 / s->fixed_scale, n);
+    return cuda_ok(cudaGetLastError(), "fold_fixed_kernel", __FILE__, __LINE__);
+}
+int photon_scene_deterministic(photon_scene *s) { return s && s->d_fixed ? 1 : 0; }
+int photon_scene_download_image_fixed(photon_scene *s, long long *h, double *scale) {
+    if (!scene_ok(s)) return 1;
+    if (!s->d_fixed) { g_error = "scene was not created with PHOTON_DETERMINISTIC=1"; return 1; }
+    if (scale) *scale = s->fixed_scale;
+    size_t bytes = (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(long long);
+    if (!cuda_ok(cudaMemcpyAsync(h, s->d_fixed, bytes, cudaMemcpyDeviceToHost, s->stream), "fixed D2H", __FILE__, __LINE__)) return 1;
+    return cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__) ? 0 : 1;
+}
 int photon_scene_download_image(photon_scene *s, float *h) {
     if (!scene_ok(s)) return 1;
+    if (!fold_fixed(s)) return 1;
     const size_t bytes = (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float);
     void *stage = g_stage.get(bytes);
     if (!cuda_ok(cudaMemcpyAsync(stage ? stage : (void *)h, s->d_image, bytes, cudaMemcpyDeviceToHost, s->stream), "image D2H", __FILE__, __LINE__)) return 1;
@@ -560,7 +605,7 @@ bool write_f3_file(const std::string &dir, const char *prefix, int k, const floa
     return true;
 }
 
-struct ShardResult { bool ok = false; std::vector<float> image; long long steps = 0, rays = 0; float ms = 0; };
+struct ShardResult { bool ok = false; std::vector<float> image; std::vector<long long> fixed; double scale = 0; };
 
 }  // namespace
 
@@ -661,14 +706,28 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
         th.emplace_back([&, g]() {
             photon_scene *s = make_scene(shard_index * ngpus + g, shard_count * ngpus, g);
             if (!s) return;
-            res[g].image.resize(npix);
-            res[g].ok = photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0 &&
-                        photon_scene_download_image(s, res[g].image.data()) == 0;
+            res[g].ok = photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
+            if (res[g].ok && photon_scene_deterministic(s)) {
+                res[g].fixed.resize(npix);
+                res[g].ok = photon_scene_download_image_fixed(s, res[g].fixed.data(), &res[g].scale) == 0;
+            } else if (res[g].ok) {
+                res[g].image.resize(npix);
+                res[g].ok = photon_scene_download_image(s, res[g].image.data()) == 0;
+            }
             photon_scene_destroy(s);
         });
     }
     for (auto &t : th) t.join();
     for (int g = 0; g < ngpus; g++) if (!res[g].ok) { fprintf(stderr, "libparallel_ray_tracing(b200): GPU %d failed; image untouched\n", g); return; }
+    if (!res[0].fixed.empty()) {          // deterministic: exact integer sum, one rounding (as on one GPU)
+        const double inv = 1.0 / res[0].scale;
+        for (size_t i = 0; i < npix; i++) {
+            long long q = 0;
+            for (int g = 0; g < ngpus; g++) q += res[g].fixed[i];
+            if (q != 0) image_array[i] += (float)((double)q * inv);
+        }
+        return;
+    }
     for (size_t i = 0; i < npix; i++) {
         float acc = image_array[i];
         for (int g = 0; g < ngpus; g++) acc += res[g].image[i];

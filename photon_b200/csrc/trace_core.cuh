@@ -41,6 +41,8 @@ struct TraceArgs {
     float pos_noise_std, ngrad_noise_std;
     // outputs
     float *image;
+    unsigned long long *image_fixed;     // deterministic mode: 64-bit fixed-point image, else null
+    double fixed_scale;                  // 2^k: increments are rounded to multiples of 1/fixed_scale
     f3 *final_pos, *final_dir;           // [n_save] or null
     long long n_save;
     f3 *inter_pos, *inter_dir;           // [n_save][n_inter] or null

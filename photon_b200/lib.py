@@ -43,6 +43,10 @@ def load_library(require_gpu=False):
             f = getattr(lib, name)
             f.argtypes = [C.c_void_p, C.c_void_p]
             f.restype = C.c_int
+        lib.photon_scene_deterministic.argtypes = [C.c_void_p]
+        lib.photon_scene_deterministic.restype = C.c_int
+        lib.photon_scene_download_image_fixed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.photon_scene_download_image_fixed.restype = C.c_int
         lib.photon_scene_image_device_ptr.argtypes = [C.c_void_p]
         lib.photon_scene_image_device_ptr.restype = C.c_void_p
         for name in ("photon_scene_ray_steps", "photon_scene_rays", "photon_scene_sensor_hits"):

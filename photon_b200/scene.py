@@ -58,6 +58,17 @@ class ResidentScene:
         self._ck(self.lib.photon_scene_download_image(self.handle, out.ctypes.data), "download_image")
         return out
 
+    @property
+    def deterministic(self):
+        return bool(self.lib.photon_scene_deterministic(self.handle))
+
+    def download_image_fixed(self):
+        """Deterministic mode: (int64 image in units of 1/scale, scale)."""
+        out = np.empty(self.shape, np.int64)
+        scale = C.c_double(0.0)
+        self._ck(self.lib.photon_scene_download_image_fixed(self.handle, out.ctypes.data, C.byref(scale)), "download_image_fixed")
+        return out, scale.value
+
     def trace(self, sync=True):
         self._ck(self.lib.photon_scene_trace(self.handle), "trace")
         if sync:
