@@ -409,6 +409,179 @@ void rk4(Ray &ray, const Field &F, const Sampler &S, v3 scale, Interm im, StepCo
     }
 }
 
+// (a9) RKF45 -- trace.h:304-718, restated literally.  The reference reads the texture's w channel
+// (n-1) where it means n: the "refractive index" of every step after the first accepted one is
+// n-1 (:683), the l terms carry n-1 (:430 ...), and the skip-ahead divides by min(n-1) (:425).
+// Scalar constants such as 3.0/32.0 are doubles narrowed to float by operator*(float, float3).
+inline v3 vabs(v3 a) { return mk(fabsf(a.x), fabsf(a.y), fabsf(a.z)); }      // float3_operators.h:79-82
+void rk45(Ray &ray, const Field &F, const Sampler &S, v3 scale, StepCount &sc) {
+    const float tol = 1e-3f;
+    float refractive_index = 1.000277f;
+    float h = F.step_size / refractive_index;
+    v3 pos = ray.pos, dir = ray.dir;
+    int loop = 0;
+    // one stage: locate R_n; outside -> shrink h by 10 and retry while h >= lim*step (:412-416)
+    auto shrink = [&](double lim) { h = (float)((double)h / 10.0); return (double)h >= lim * (double)F.step_size; };
+    while (true) {
+        loop += 1;
+        if (loop > 100000) break;
+        v3 R_n = pos;
+        v3 T_n = refractive_index * dir;
+        v3 k1 = h * T_n;
+        v3 l = lookup_index(R_n, F, scale);
+        if (!inside_box(R_n, F, l)) { if (shrink(0.1)) continue; else break; }
+        v4 val = tex3d(S, l.x, l.y, l.z);
+        if (val.w < F.data_min) {                                        // :423-428
+            pos = pos + F.step_size / F.data_min * dir;
+            ray.pos = pos;
+            continue;
+        }
+        v3 l1 = h * val.w * mk(val.x, val.y, val.z);
+        R_n = pos + k1 / 4.0f;                                           // :437
+        T_n = refractive_index * dir + l1 / 4.0f;
+        v3 k2 = h * T_n;
+        l = lookup_index(R_n, F, scale);
+        if (!inside_box(R_n, F, l)) { if (shrink(0.1)) continue; else break; }
+        val = tex3d(S, l.x, l.y, l.z);
+        v3 l2 = h * val.w * mk(val.x, val.y, val.z);
+        const float c31 = (float)(3.0 / 32.0), c32 = (float)(9.0 / 32.0);
+        R_n = pos + c31 * k1 + c32 * k2;                                 // :478
+        T_n = refractive_index * dir + c31 * l1 + c32 * l2;
+        v3 k3 = h * T_n;
+        l = lookup_index(R_n, F, scale);
+        if (!inside_box(R_n, F, l)) { if (shrink(0.1)) continue; else break; }
+        val = tex3d(S, l.x, l.y, l.z);
+        v3 l3 = h * val.w * mk(val.x, val.y, val.z);
+        const float c41 = (float)(1932.0 / 2197.0), c42 = (float)(7200.0 / 2197.0), c43 = (float)(7296.0 / 2197.0);
+        R_n = pos + c41 * k1 - c42 * k2 + c43 * k3;                      // :521
+        T_n = refractive_index * dir + c41 * l1 - c42 * l2 + c43 * l3;
+        v3 k4 = h * T_n;
+        l = lookup_index(R_n, F, scale);
+        if (!inside_box(R_n, F, l)) { if (shrink(0.1)) continue; else break; }
+        val = tex3d(S, l.x, l.y, l.z);
+        v3 l4 = h * val.w * mk(val.x, val.y, val.z);
+        const float c51 = (float)(439.0 / 216.0), c52 = 8.0f, c53 = (float)(3680.0 / 513.0), c54 = (float)(845.0 / 4104.0);
+        R_n = pos + c51 * k1 - c52 * k2 + c53 * k3 - c54 * k4;           // :565
+        T_n = refractive_index * dir + c51 * l1 - c52 * l2 + c53 * l3 - c54 * l4;
+        v3 k5 = h * T_n;
+        l = lookup_index(R_n, F, scale);
+        if (!inside_box(R_n, F, l)) { if (shrink(0.1)) continue; else break; }
+        val = tex3d(S, l.x, l.y, l.z);
+        v3 l5 = h * val.w * mk(val.x, val.y, val.z);
+        const float c61 = (float)(8.0 / 27.0), c62 = 2.0f, c63 = (float)(3544.0 / 2565.0), c64 = (float)(1859.0 / 4104.0),
+                    c65 = (float)(11.0 / 40.0);
+        R_n = pos - c61 * k1 + c62 * k2 - c63 * k3 + c64 * k4 - c65 * k5;   // :609
+        T_n = refractive_index * dir - c61 * l1 + c62 * l2 - c63 * l3 + c64 * l4 - c65 * l5;
+        v3 k6 = h * T_n;
+        l = lookup_index(R_n, F, scale);
+        if (!inside_box(R_n, F, l)) { if (shrink(0.01)) continue; else break; }   // :635
+        val = tex3d(S, l.x, l.y, l.z);
+        v3 l6 = h * val.w * mk(val.x, val.y, val.z);
+        const float a1 = (float)(25.0 / 216.0), a3 = (float)(1408.0 / 2565.0), a4 = (float)(2197.0 / 4104.0), a5 = (float)(1.0 / 5.0);
+        const float b1 = (float)(16.0 / 135.0), b3 = (float)(6656.0 / 12825.0), b4 = (float)(28561.0 / 56430.0),
+                    b5 = (float)(9.0 / 50.0), b6 = (float)(2.0 / 55.0);
+        (void)k6;
+        v3 y4 = pos + a1 * k1 + a3 * k3 + a4 * k4 - a5 * k5;             // :646-650
+        v3 y5 = pos + b1 * k1 + b3 * k3 + b4 * k4 - b5 * k5 + b6 * k6;
+        v3 z4 = refractive_index * dir + a1 * l1 + a3 * l3 + a4 * l4 - a5 * l5;
+        v3 z5 = refractive_index * dir + b1 * l1 + b3 * l3 + b4 * l4 - b5 * l5 + b6 * l6;
+        float inv_h = 1 / h;
+        v3 R0 = inv_h * vabs(y4 - y5), R1 = inv_h * vabs(z4 - z5);
+        float a = R0.x > R1.x ? R0.x : R1.x, b = R0.y > R1.y ? R0.y : R1.y, c = R0.z > R1.z ? R0.z : R1.z;
+        float R_max = (a > b ? a : b) > c ? (a > b ? a : b) : c;
+        float s = (float)(0.84 * (double)powf(tol / R_max, 0.25f));      // :663
+        if (R_max <= tol) {
+            pos = y4;
+            dir = (1 / refractive_index) * z4;
+            dir = normalize(dir);
+            ray.pos = pos; ray.dir = dir;
+            sc.steps++;
+            l = lookup_index(pos, F, scale);
+            if (!inside_box(pos, F, l)) return;
+            val = tex3d(S, l.x, l.y, l.z);
+            refractive_index = val.w;                                    // :683 (n-1, as the reference)
+            if ((double)s > 5.00) s = 5.00f;
+            h *= s;
+        } else {
+            if ((double)s < 0.1) s = (float)0.1;
+            h *= s;
+        }
+    }
+}
+
+// (a9) Adams-Bashforth 4 bootstrapped by three RK4 steps -- trace.h:1293-1453, restated literally
+// (w = n-1 is used as the index throughout, as the reference does).  The reference leaves its history
+// arrays and T_n uninitialised when the bootstrap ends early (a ray that leaves the box within three
+// steps): undefined there, zero here.
+void adams_bashforth(Ray &ray, const Field &F, const Sampler &S, v3 scale, StepCount &sc) {
+    v3 pos = ray.pos, dir = ray.dir;
+    v4 val{0, 0, 0, 0};
+    v3 R_n = mk(0, 0, 0), T_n = mk(0, 0, 0), D = mk(0, 0, 0);
+    v3 Dp[3] = {mk(0, 0, 0), mk(0, 0, 0), mk(0, 0, 0)}, Tp[3] = {mk(0, 0, 0), mk(0, 0, 0), mk(0, 0, 0)};
+    const float sixth = (float)(1 / 6.0);
+    int loop = 0;
+    long long guard = 0;
+    while (loop < 3) {
+        if (++guard > 10000000) break;                                   // (the reference has no guard here)
+        pos = ray.pos; dir = ray.dir;
+        v3 l = lookup_index(pos, F, scale);
+        if (!inside_box(pos, F, l)) break;
+        if (!lookup_ok(l, F)) { pos = pos + F.step_size / F.data_min * dir; ray.pos = pos; continue; }   // :1330-1336
+        val = tex3d(S, l.x, l.y, l.z);
+        if (val.w < F.data_min) { pos = pos + F.step_size / F.data_min * dir; ray.pos = pos; continue; }
+        R_n = pos;
+        float dt = F.step_size / val.w;
+        T_n = val.w * ray.dir;
+        D = mk(val.w * val.x, val.w * val.y, val.w * val.z);
+        v3 A = dt * D;
+        pos = R_n + (float)((double)dt / 2.0) * T_n + (float)(1 / 8.0 * (double)dt) * A;   // :1363
+        l = lookup_index(pos, F, scale);
+        if (!inside_box(pos, F, l)) break;
+        val = tex3d(S, l.x, l.y, l.z);
+        D = mk(val.w * val.x, val.w * val.y, val.w * val.z);
+        v3 B = dt * D;
+        pos = R_n + dt * T_n + (float)(1 / 2.0 * (double)dt) * B;        // :1373
+        l = lookup_index(pos, F, scale);
+        if (!inside_box(pos, F, l)) break;
+        val = tex3d(S, l.x, l.y, l.z);
+        D = mk(val.w * val.x, val.w * val.y, val.w * val.z);
+        v3 C = dt * D;
+        R_n = R_n + dt * (T_n + sixth * (A + 2.0f * B));
+        T_n = T_n + sixth * (A + 4.0f * B + C);
+        ray.pos = R_n;
+        ray.dir = normalize(T_n / val.w);
+        Tp[loop] = T_n; Dp[loop] = D;
+        loop += 1; sc.steps++;
+    }
+    float refractive_index = val.w;
+    pos = ray.pos; dir = ray.dir;
+    guard = 0;
+    while (true) {
+        if (++guard > 10000000) break;
+        R_n = ray.pos;
+        v3 l = lookup_index(R_n, F, scale);
+        if (!inside_box(R_n, F, l)) break;
+        val = tex3d(S, l.x, l.y, l.z);
+        if (val.w < F.data_min) {                                        // :1417-1422
+            pos = pos + F.step_size / refractive_index * dir;
+            ray.pos = pos;
+            continue;
+        }
+        float dt = F.step_size / val.w;
+        D = mk(val.w * val.x, val.w * val.y, val.w * val.z);
+        float d24 = dt / 24;
+        v3 R1 = R_n + d24 * (55.0f * T_n - 59.0f * Tp[2] + 37.0f * Tp[1] - 9.0f * Tp[0]);   // :1430
+        v3 T1 = T_n + d24 * (55.0f * D - 59.0f * Dp[2] + 37.0f * Dp[1] - 9.0f * Dp[0]);     // :1432
+        Tp[0] = Tp[1]; Dp[0] = Dp[1];
+        Tp[1] = Tp[2]; Dp[1] = Dp[2];
+        Tp[2] = T_n; Dp[2] = D;
+        R_n = R1; T_n = T1;
+        ray.pos = R_n;
+        ray.dir = normalize(T_n / val.w);
+        sc.steps++;
+    }
+}
+
 // (a4) trace.h:1455-1544
 void trace_volume(Ray &ray, const Field &F, const Sampler &S, int algorithm, bool ngrad_noise,
                   float ngrad_std, NoiseGen &ng, Interm im, StepCount &sc) {
@@ -422,7 +595,9 @@ void trace_volume(Ray &ray, const Field &F, const Sampler &S, int algorithm, boo
     switch (algorithm) {
         case 1: euler(ray, F, S, scale, ngrad_noise, ngrad_std, ng, im, sc); break;
         case 2: rk4(ray, F, S, scale, im, sc); break;
-        default: break;   // 3 (rk45) and 4 (adams-bashforth): not restated yet -> pass-through
+        case 3: rk45(ray, F, S, scale, sc); break;
+        case 4: adams_bashforth(ray, F, S, scale, sc); break;
+        default: break;
     }
 }
 

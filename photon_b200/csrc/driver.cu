@@ -347,9 +347,6 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         const char *smp = getenv("PHOTON_SAMPLER");
         s->use_texture = smp && strcmp(smp, "texture") == 0;
         if (s->use_texture && !ensure_texture(*s->field, s->stream)) return false;
-        if (algorithm == 3 || algorithm == 4)
-            fprintf(stderr, "libparallel_ray_tracing(b200): ray_tracing_algorithm %d (rk45/adams-bashforth) is not "
-                            "implemented yet; rays pass the volume undeflected\n", algorithm);
     }
 
     // ---- image + counters

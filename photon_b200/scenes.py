@@ -154,13 +154,16 @@ def constant_gradient_slab(n, spacing, drho_dx, rho0=1.225):
 
 
 def c3_bos(nrrd_path, *, n=512, dots_per_side=100, points_per_dot=100, rays_per_point=1000,
-           nx=1024, ny=1024, algorithm=2, write_field=True, source_point_number=10000):
+           nx=1024, ny=1024, algorithm=2, write_field=True, source_point_number=10000, field_z_centre=0.0,
+           blob_amplitude=0.5):
     """BOS through a Gaussian density blob on an n^3 NRRD grid.
 
     Geometry of sample-data/bos/sample-parameters.mat with y_camera_angle = 0: f = 105 mm,
     f/11, object distance 1e6 um, thin lens, pixel pitch 10 um, diffraction 3 px,
     ray_cone_pitch_ratio 1e-4, RK4.  Field extent 89 936 um regardless of n (spacing scales),
-    sigma = 15 mm, centred at the volume-frame origin (NRRD z origin = 750e3 - extent/2).
+    sigma = 15 mm, centred at the volume-frame origin (NRRD z origin = 750e3 - extent/2), or at
+    volume-frame z = field_z_centre (the dots sit at z = +250 mm; a box that encloses them makes rays
+    start inside the field, which is the only way the reference's rk45 / adams-bashforth integrate).
     """
     from .nrrd import write_nrrd
     call = RayTracingCall()
@@ -170,8 +173,8 @@ def c3_bos(nrrd_path, *, n=512, dots_per_side=100, points_per_dot=100, rays_per_
     extent = 511 * 176.0
     spacing = extent / (n - 1)
     if write_field:
-        rho = gaussian_blob(n, spacing, 15e3)
-        write_nrrd(nrrd_path, rho, (spacing,) * 3, (-extent / 2, -extent / 2, 750e3 - extent / 2))
+        rho = gaussian_blob(n, spacing, 15e3, amp=blob_amplitude)
+        write_nrrd(nrrd_path, rho, (spacing,) * 3, (-extent / 2, -extent / 2, 750e3 + field_z_centre - extent / 2))
     bos_dots(call, z_object, dots_per_side=dots_per_side, extent=40e3,
              points_per_dot=points_per_dot, dot_diameter=300.0)
     call.lightray_number_per_particle = rays_per_point

@@ -15,7 +15,8 @@ def cases(tmp_path_factory):
 
 CASE_NAMES = ["bos_rk4_thin_diffraction", "bos_euler_thin_diffraction", "bos_nogradient",
               "bos_rk4_multibatch_ragged", "piv_mie_thick_bilinear", "piv_diffuse_thin_bilinear",
-              "piv_apparent", "piv_mie_thick_diffraction", "piv_chief_ray_only"]
+              "piv_apparent", "piv_mie_thick_diffraction", "piv_chief_ray_only",
+              "bos_rk45_thin_diffraction", "bos_ab4_thin_diffraction"]
 
 
 @pytest.mark.parametrize("name", CASE_NAMES)

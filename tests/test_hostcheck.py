@@ -15,7 +15,7 @@ def cases(tmp_path_factory):
 @pytest.mark.parametrize("name", ["bos_rk4_thin_diffraction", "bos_euler_thin_diffraction", "bos_nogradient",
                                   "bos_rk4_multibatch_ragged", "piv_mie_thick_bilinear",
                                   "piv_diffuse_thin_bilinear", "piv_apparent", "piv_mie_thick_diffraction",
-                                  "piv_chief_ray_only"])
+                                  "piv_chief_ray_only", "bos_rk45_thin_diffraction", "bos_ab4_thin_diffraction"])
 def test_stage_code_bit_exact_vs_oracle(name, cases, hostcheck_lib, oracle_lib, tmp_path):
     call, pitch = cases[name]
     (tmp_path / "o").mkdir()

@@ -105,6 +105,13 @@ def parity_cases(tmpdir):
     c.camera.implement_diffraction = True
     c.camera.diffraction_diameter = 3.0
     cases["piv_mie_thick_diffraction"] = (c, 17.0)
+    nrrd2 = os.path.join(str(tmpdir), "blob64_around_dots.nrrd")      # rays start inside the field
+    c = scenes.c3_bos(nrrd2, n=64, dots_per_side=10, points_per_dot=10, rays_per_point=20, algorithm=3, field_z_centre=220e3,
+                      blob_amplitude=2e-4)    # their deflection is ~1/(n-1) too strong: weak blob keeps rays on the sensor
+    cases["bos_rk45_thin_diffraction"] = (c, 10.0)      # trace.h:304-718
+    c = scenes.c3_bos(nrrd2, n=64, dots_per_side=10, points_per_dot=10, rays_per_point=20, write_field=False, algorithm=4,
+                      field_z_centre=220e3)
+    cases["bos_ab4_thin_diffraction"] = (c, 10.0)       # trace.h:1293-1453
     c = scenes.c1_piv(particles=40, rays_per_particle=1)
     cases["piv_chief_ray_only"] = (c, 17.0)             # rpp == 1 -> chief ray (prt.cu:111-116)
     return cases
