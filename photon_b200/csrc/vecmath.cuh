@@ -39,6 +39,8 @@ PH_HD float add_rn(float a, float b) {
 #endif
 }
 
+PH_HD float mad_rn(float a, float b, float c) { return add_rn(mul_rn(a, b), c); }   // a*b + c, two roundings
+
 // f3: every multiply and add is rounded on its own (no FMA contraction), whatever the compiler
 // flags.  The per-ray stages -- generation, frame rotations, lens, sensor -- work in float32 at
 // |coordinates| ~ 1e6 um where sums cancel catastrophically (ray-sphere quadratic
