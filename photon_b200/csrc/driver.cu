@@ -256,7 +256,9 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         if (s->d_fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->d_fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (s->occupancy >= 4) trace_rays_kernel<false, 4, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (s->occupancy == 5) trace_rays_kernel<false, 5, LinearField, false, 128><<<grid, 128, 0, s->stream>>>(a, S);   // 96 regs, 20 warps/SM
+        else if (s->occupancy == 6) trace_rays_kernel<false, 3, LinearField, false, 192><<<grid, 192, 0, s->stream>>>(a, S);   // 112 regs, 18 warps/SM
+        else if (s->occupancy == 4) trace_rays_kernel<false, 4, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->occupancy == 3) trace_rays_kernel<false, 3, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     }
@@ -381,8 +383,8 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
     // persistent grid: a multiple of the SM count (148 on B200), 2 CTAs resident per SM
     int sm_count = 148;
     CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device));
-    if (const char *o = getenv("PHOTON_OCC")) s->occupancy = std::max(2, std::min(4, atoi(o)));
-    int mult = s->occupancy * 4;
+    if (const char *o = getenv("PHOTON_OCC")) s->occupancy = std::max(2, std::min(6, atoi(o)));
+    int mult = (s->occupancy == 6 ? 3 : s->occupancy) * 4;
     if (const char *g = getenv("PHOTON_GRID_MULT")) mult = std::max(1, atoi(g));
     s->grid_blocks = sm_count * mult;
     CK(cudaStreamSynchronize(s->stream));

@@ -74,7 +74,8 @@ def assert_parity(name, m):
         assert m["dpos_px_p999"] <= TOL_POS_PX and m["dpos_px"] <= THICK_LENS_MAX_PX, m
     elif name in AB4_CASES:
         assert m["dpos_px_p99"] <= TOL_POS_PX and m["dpos_px"] <= AB4_MAX_PX, m
-        m = dict(m, image_rel_l2=min(m["image_rel_l2"], TOL_IMG_L2) if m["image_rel_l2"] <= 5e-3 else m["image_rel_l2"])
+        assert m["ddir_rad"] <= TOL_DIR_RAD and m["image_rel_l2"] <= 5e-3, m      # image: those few rays
+        return
     else:
         assert m["dpos_px"] <= TOL_POS_PX, m
     assert m["ddir_rad"] <= TOL_DIR_RAD, m
