@@ -30,8 +30,14 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-FLOP_PER_RAY_STEP = 330.0        # RK4 + trilinear float4, SURVEY.md 8(d) / BASELINE.md 3
-L1_BYTES_PER_RAY_STEP = 384.0    # 3 samples x 8 texels x 16 B
+CUBIC = os.environ.get("PHOTON_INTERPOLATION", "linear") == "cubic"
+# RK4 + trilinear float4: SURVEY.md 8(d) / BASELINE.md 3.  RK4 + tricubic B-spline on scalar coefficients
+# (PHOTON_INTERPOLATION=cubic): 3 x (9 coordinate + 40 weights + 192 FMA x 2) + 135 = 1434, 3 x 64 taps x 4 B.
+FLOP_PER_RAY_STEP = 1434.0 if CUBIC else 330.0
+L1_BYTES_PER_RAY_STEP = 768.0 if CUBIC else 384.0    # linear: 3 samples x 8 texels x 16 B
+# dram__bytes_read.sum + dram__bytes_write.sum of one trace launch from the ncu --set full capture under
+# profiles/ (r1j, default variant, linear mode); None where no capture of this mode exists
+NCU_DRAM_BYTES_PER_LAUNCH = None if CUBIC else None
 
 
 def parse():
@@ -178,10 +184,11 @@ def run_reference_arm(args):
 
 
 def workload_config(args, call):
-    return {"workload": f"C3 BOS Gaussian blob {args.grid}^3 NRRD, {args.sensor}x{args.sensor} sensor, RK4 + trilinear, "
+    return {"workload": f"C3 BOS Gaussian blob {args.grid}^3 NRRD, {args.sensor}x{args.sensor} sensor, RK4 + {'tricubic B-spline (scalar coefficients)' if CUBIC else 'trilinear'}, "
                         f"thin lens f/11, diffraction 3 px, {call.num_particles} source points x {args.rays_per_point} rays",
             "rays_per_step": args.points_per_step * args.rays_per_point, "points_per_step": args.points_per_step,
-            "field_bytes": 16 * args.grid ** 3, "rng": os.environ.get("PHOTON_RNG", "reference"),
+            "field_bytes": 16 * args.grid ** 3, "coefficient_bytes": 4 * args.grid ** 3 if CUBIC else 0,
+            "interpolation": "cubic" if CUBIC else "linear", "rng": os.environ.get("PHOTON_RNG", "reference"),
             "sampler": os.environ.get("PHOTON_SAMPLER", "linear"),
             "l2_policy": "field (2 GiB at 512^3) is larger than the 126 MB L2; consecutive steps trace different batches"}
 
@@ -315,8 +322,9 @@ def main():
             "clocks": clocks.summary(),
             "e2e": e2e,
             "roofline": {"bound": "fp32_issue", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": achieved_tf / fp32_peak if fp32_peak and fp32_peak > 0 else None, "traffic": None,
-                         "kernel": "trace_rays_kernel<LinearField>", "kernel_ms": k_ms,
+                         "frac": achieved_tf / fp32_peak if fp32_peak and fp32_peak > 0 else None,
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
+                         "kernel": "trace_rays_kernel<BSplineField>" if CUBIC else "trace_rays_kernel<LinearField>", "kernel_ms": k_ms,
                          "flop_per_ray_step": FLOP_PER_RAY_STEP, "ray_steps_per_launch": steps_per_launch,
                          "peak_source": "FFMA loop measured live on this GPU (photon_b200_measure_fp32_tflops); "
                                         "MEASURED_PEAKS.json has no FP32 figure",

@@ -104,6 +104,14 @@ int       photon_scene_num_points(photon_scene *s);     /* source points in this
  * out may be NULL to query the size. */
 int photon_b200_load_field(const char *path, float meta16[16], float *out_float4, long long capacity_voxels);
 
+/* Cubic mode (PHOTON_INTERPOLATION=cubic): the B-spline coefficient volume of n-1 (float[D][H][W]),
+ * prefiltered on the GPU (replaces CubicBSplinePrefilter3DTimer, trace.h:1655).  out may be NULL. */
+int photon_b200_load_coefficients(const char *path, float *out, long long capacity_voxels);
+/* One field sample per point at texel coordinates xyz_texel[3n] (the convention of tex3D in
+ * trace.h:1052: texel centres at +0.5, clamp addressing) -> out4[4n] = (dn/dx, dn/dy, dn/dz, n-1).
+ * cubic = 0: trilinear blend of the (grad n, n-1) texels; 1: tricubic B-spline with analytic gradient. */
+int photon_b200_sample_field(const char *path, int cubic, int n, const float *xyz_texel, float *out4);
+
 /* FP32 FMA throughput of the device in TFLOP/s, measured with a register-resident FFMA loop
  * (the roofline denominator for the trace kernel, which is FP32-issue bound, not HBM bound). */
 double photon_b200_measure_fp32_tflops(int device);

@@ -155,8 +155,9 @@ Ray generate_ray(float lens_pitch, float image_distance, const scattering_data_t
 struct Field {
     v3 min_bound, max_bound, spacing;
     int W = 0, H = 0, D = 0;
-    float step_size = 0, data_min = 0;
+    float step_size = 0, data_min = 0, data_min_samples = FLT_MAX;
     std::vector<v4> g;   // (dn/dx, dn/dy, dn/dz, n-1), x fastest
+    std::vector<float> coef;   // cubic mode: B-spline coefficients of n-1 (prefiltered), x fastest
 };
 
 bool load_field(const char *path, Field &F, std::string &err) {
@@ -213,12 +214,61 @@ bool load_field(const char *path, Field &F, std::string &err) {
 }
 
 // ---------------------------------------------------------------------------
+// Cubic mode (PHOTON_INTERPOLATION=cubic): tricubic B-spline interpolation of n-1 with analytic
+// gradient.  The reference carries such a branch (trace.h:896-946, 1184-1279, Host_Init :1648-1660 on
+// top of CubicInterpolationCUDA) but hard-codes interpolation_scheme = 1 (prt.cu:3330), so it cannot
+// be reached through the ABI: there is no reference output to pin this mode against -- PARITY UNPINNED.
+// What is restated is CI's published algorithm (Ruijters & Thevenaz, Comput. J. 55, 2012):
+//   prefilter  = CubicInterpolationCUDA/code/internal/cubicPrefilter_kernel.cu:52-113 along x, y, z
+//   weights    = internal/bspline_kernel.cu:83-104 (value and first derivative)
+//   evaluation = the 64-tap separable sum that cubicTex3D_kernel.cu:50-82 computes through 8 linear
+//                fetches, with the same coordinate convention (texel centres at +0.5, clamp addressing)
+// on a SCALAR volume (4 B/voxel instead of the float4 gradient texels), gradient = d/d(texel) / spacing.
+// ---------------------------------------------------------------------------
+void prefilter_line(float *c, size_t n, size_t stride) {
+    const float pole = sqrtf(3.0f) - 2.0f;
+    const float lambda = (1.0f - pole) * (1.0f - 1.0f / pole);
+    size_t horizon = n < 12 ? n : 12;
+    float zn = pole, sum = c[0];
+    for (size_t k = 0; k < horizon; k++) { sum += zn * c[k * stride]; zn *= pole; }
+    float prev = lambda * sum;
+    c[0] = prev;
+    for (size_t k = 1; k < n; k++) { prev = lambda * c[k * stride] + pole * prev; c[k * stride] = prev; }
+    prev = (pole / (pole - 1.0f)) * c[(n - 1) * stride];
+    c[(n - 1) * stride] = prev;
+    for (size_t k = n - 1; k-- > 0;) { prev = pole * (prev - c[k * stride]); c[k * stride] = prev; }
+}
+void build_coefficients(Field &F) {
+    size_t W = F.W, H = F.H, D = F.D;
+    F.coef.resize(W * H * D);
+    for (size_t i = 0; i < W * H * D; i++) F.coef[i] = F.g[i].w;
+#pragma omp parallel for schedule(static)
+    for (size_t l = 0; l < H * D; l++) prefilter_line(&F.coef[l * W], W, 1);
+#pragma omp parallel for schedule(static)
+    for (size_t l = 0; l < W * D; l++) prefilter_line(&F.coef[(l / W) * W * H + (l % W)], H, W);
+#pragma omp parallel for schedule(static)
+    for (size_t l = 0; l < W * H; l++) prefilter_line(&F.coef[l], D, W * H);
+}
+inline void bspline_w(float t, float *w, float *d) {
+    const float one = 1.0f - t, sq = t * t, osq = one * one;
+    const float sixth = 1.0f / 6.0f, two3 = 2.0f / 3.0f;
+    w[0] = sixth * osq * one;
+    w[1] = two3 - 0.5f * sq * (2.0f - t);
+    w[2] = two3 - 0.5f * osq * (2.0f - one);
+    w[3] = sixth * sq * t;
+    d[0] = -0.5f * sq + t - 0.5f;
+    d[1] = 1.5f * sq - 2.0f * t;
+    d[2] = -1.5f * sq + t + 0.5f;
+    d[3] = 0.5f * sq;
+}
+
+// ---------------------------------------------------------------------------
 // Software tex3D: unnormalised coordinates, texel centres at +0.5, clamp addressing,
 // linear filter (Host_Init, trace.h:1620-1642; CUDA Programming Guide "Linear Filtering":
 // xB = x-0.5, i = floor(xB), alpha = frac(xB) kept in 1.8 fixed point).
 // weight_bits = 0 -> exact float fractions; 8 -> hardware-like 8 fractional bits.
 // ---------------------------------------------------------------------------
-struct Sampler { const Field *F; int weight_bits; };
+struct Sampler { const Field *F; int weight_bits; bool cubic = false; };
 
 inline float quant(float a, int bits) {
     if (bits <= 0) return a;
@@ -227,8 +277,40 @@ inline float quant(float a, int bits) {
 }
 inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
+v4 cubic_tex3d(const Field &F, float x, float y, float z) {
+    float xb = x - 0.5f, yb = y - 0.5f, zb = z - 0.5f;
+    float fx = floorf(xb), fy = floorf(yb), fz = floorf(zb);
+    float wx[4], dx[4], wy[4], dy[4], wz[4], dz[4];
+    bspline_w(xb - fx, wx, dx); bspline_w(yb - fy, wy, dy); bspline_w(zb - fz, wz, dz);
+    int i = (int)fx, j = (int)fy, k = (int)fz;
+    size_t W = F.W, WH = (size_t)F.W * F.H;
+    int ii[4], jj[4], kk[4];
+    for (int t = 0; t < 4; t++) {
+        ii[t] = clampi(i - 1 + t, 0, F.W - 1); jj[t] = clampi(j - 1 + t, 0, F.H - 1); kk[t] = clampi(k - 1 + t, 0, F.D - 1);
+    }
+    float v[4], vx[4], vy[4];
+    for (int c = 0; c < 4; c++) {
+        float s[4], sx[4];
+        for (int b = 0; b < 4; b++) {
+            const float *row = &F.coef[kk[c] * WH + jj[b] * W];
+            float c0 = row[ii[0]], c1 = row[ii[1]], c2 = row[ii[2]], c3 = row[ii[3]];
+            s[b] = wx[3] * c3 + (wx[2] * c2 + (wx[1] * c1 + wx[0] * c0));
+            sx[b] = dx[3] * c3 + (dx[2] * c2 + (dx[1] * c1 + dx[0] * c0));
+        }
+        v[c] = wy[3] * s[3] + (wy[2] * s[2] + (wy[1] * s[1] + wy[0] * s[0]));
+        vx[c] = wy[3] * sx[3] + (wy[2] * sx[2] + (wy[1] * sx[1] + wy[0] * sx[0]));
+        vy[c] = dy[3] * s[3] + (dy[2] * s[2] + (dy[1] * s[1] + dy[0] * s[0]));
+    }
+    float val = wz[3] * v[3] + (wz[2] * v[2] + (wz[1] * v[1] + wz[0] * v[0]));
+    float gx = wz[3] * vx[3] + (wz[2] * vx[2] + (wz[1] * vx[1] + wz[0] * vx[0]));
+    float gy = wz[3] * vy[3] + (wz[2] * vy[2] + (wz[1] * vy[1] + wz[0] * vy[0]));
+    float gz = dz[3] * v[3] + (dz[2] * v[2] + (dz[1] * v[1] + dz[0] * v[0]));
+    return v4{gx * (1.0f / F.spacing.x), gy * (1.0f / F.spacing.y), gz * (1.0f / F.spacing.z), val};
+}
+
 v4 tex3d(const Sampler &S, float x, float y, float z) {
     const Field &F = *S.F;
+    if (S.cubic) return cubic_tex3d(F, x, y, z);
     float xb = x - 0.5f, yb = y - 0.5f, zb = z - 0.5f;
     float fx = floorf(xb), fy = floorf(yb), fz = floorf(zb);
     float a = quant(xb - fx, S.weight_bits), b = quant(yb - fy, S.weight_bits), c = quant(zb - fz, S.weight_bits);
@@ -869,6 +951,26 @@ int photon_oracle_load_field(const char *path, float *meta16, float *out, long l
     return 0;
 }
 
+/* Cubic mode checkers: the coefficient volume and single samples at texel coordinates (cubic = 0: tex3d). */
+int photon_oracle_load_coefficients(const char *path, float *out, long long capacity_voxels) {
+    Field F; std::string err;
+    if (!load_field(path, F, err)) { fprintf(stderr, "photon_oracle: %s\n", err.c_str()); return 1; }
+    build_coefficients(F);
+    if (out && capacity_voxels >= (long long)F.coef.size()) memcpy(out, F.coef.data(), F.coef.size() * sizeof(float));
+    return 0;
+}
+int photon_oracle_sample_field(const char *path, int cubic, int n, const float *xyz, float *out4) {
+    Field F; std::string err;
+    if (!load_field(path, F, err)) { fprintf(stderr, "photon_oracle: %s\n", err.c_str()); return 1; }
+    if (cubic) build_coefficients(F);
+    Sampler S{&F, 0, cubic != 0};
+    for (int i = 0; i < n; i++) {
+        v4 v = tex3d(S, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+        out4[4 * i] = v.x; out4[4 * i + 1] = v.y; out4[4 * i + 2] = v.z; out4[4 * i + 3] = v.w;
+    }
+    return 0;
+}
+
 /* glibc lens-sample table of the reference: srand(10); interleaved rand() -- prt.cu:3228-3236 */
 void photon_oracle_lens_samples(int n, float *r1, float *r2) {
     srand(10);
@@ -936,7 +1038,16 @@ void start_ray_tracing(float lens_pitch, float image_distance,
         }
         F_cache_path = field_key;
     }
-    const Field &F = F_cache; Sampler S{&F, weight_bits};
+    const char *interp = getenv("PHOTON_INTERPOLATION");   // "linear" (default, the reference) | "cubic"
+    const bool cubic = simulate_density_gradients && interp && strcmp(interp, "cubic") == 0;
+    if (simulate_density_gradients) {
+        if (F_cache.data_min_samples == FLT_MAX) F_cache.data_min_samples = F_cache.data_min;
+        if (cubic && F_cache.coef.empty()) build_coefficients(F_cache);
+        // the spline of a constant region reproduces it to rounding only: keep the "below the global
+        // minimum" fallback (trace.h:1056) from firing on the last bit
+        F_cache.data_min = cubic ? F_cache.data_min_samples - 1e-4f * fabsf(F_cache.data_min_samples) : F_cache.data_min_samples;
+    }
+    const Field &F = F_cache; Sampler S{&F, weight_bits, cubic};
 
     int spn = src.source_point_number;
     if (np < spn) spn = np;                                              // :3366-3368

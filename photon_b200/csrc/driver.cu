@@ -51,6 +51,7 @@ struct DeviceField {
     FieldParams P{};
     f3 spacing{};
     f4 *lin = nullptr;                   // [D][H][W] float4 (grad n, n-1)
+    float *coef = nullptr;               // cubic mode: [D][H][W] B-spline coefficients of n-1 (built on demand)
     cudaArray_t arr = nullptr;           // optional 3-D array for the texture path
     cudaTextureObject_t tex = 0;
     void release() {
@@ -58,7 +59,8 @@ struct DeviceField {
         if (tex) cudaDestroyTextureObject(tex);
         if (arr) cudaFreeArray(arr);
         if (lin) cudaFree(lin);
-        tex = 0; arr = nullptr; lin = nullptr; device = -1; path.clear();
+        if (coef) cudaFree(coef);
+        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; device = -1; path.clear();
     }
 };
 std::mutex g_field_mutex;
@@ -131,6 +133,22 @@ bool ensure_texture(DeviceField &F, cudaStream_t st) {
     td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
     td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
     CK(cudaCreateTextureObject(&F.tex, &rd, &td, nullptr));
+    CK(cudaStreamSynchronize(st));
+    return true;
+}
+
+bool ensure_coefficients(DeviceField &F, cudaStream_t st) {
+    if (F.coef) return true;
+    size_t n = (size_t)F.P.W * F.P.H * F.P.D;
+    CK(cudaMalloc(&F.coef, n * sizeof(float)));
+    int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)148 * 16);
+    extract_nm1_kernel<<<blocks, 256, 0, st>>>(F.lin, F.coef, n);
+    for (int axis = 0; axis < 3; axis++) {
+        size_t lines = axis == 0 ? (size_t)F.P.H * F.P.D : axis == 1 ? (size_t)F.P.W * F.P.D : (size_t)F.P.W * F.P.H;
+        int b = (int)std::min<size_t>((lines + 127) / 128, (size_t)148 * 16);
+        prefilter_kernel<<<b, 128, 0, st>>>(F.coef, F.P.W, F.P.H, F.P.D, axis);
+    }
+    CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));
     return true;
 }
@@ -209,6 +227,7 @@ struct photon_scene {
     TraceArgs args{};
     DeviceField *field = nullptr;
     bool use_texture = false;
+    bool use_cubic = false;              // PHOTON_INTERPOLATION=cubic
     int npoints = 0, point_offset = 0;   // shard of the caller's source points
     int total_points = 0, source_point_number = 0;
     float *d_sx = nullptr, *d_sy = nullptr, *d_sz = nullptr; double *d_srad = nullptr; int *d_sdiam = nullptr;
@@ -246,7 +265,13 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     const bool dump = fpos != nullptr || ipos != nullptr;
     int grid = std::min(point_count, s->grid_blocks);
     if (s->use_texture && s->d_fixed) { g_error = "PHOTON_DETERMINISTIC is not available with PHOTON_SAMPLER=texture"; return false; }
-    if (s->use_texture) {
+    if (s->use_cubic && s->d_fixed) { g_error = "PHOTON_DETERMINISTIC is not available with PHOTON_INTERPOLATION=cubic"; return false; }
+    if (s->use_cubic) {
+        BSplineField S; S.c = s->field->coef; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
+        S.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
+        if (dump) trace_rays_kernel<true, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else trace_rays_kernel<false, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+    } else if (s->use_texture) {
         TextureField S; S.tex = s->field->tex;
         if (dump) trace_rays_kernel<true, 2, TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
@@ -349,6 +374,16 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         const char *smp = getenv("PHOTON_SAMPLER");
         s->use_texture = smp && strcmp(smp, "texture") == 0;
         if (s->use_texture && !ensure_texture(*s->field, s->stream)) return false;
+        const char *ip = getenv("PHOTON_INTERPOLATION");
+        s->use_cubic = ip && strcmp(ip, "cubic") == 0;
+        if (s->use_cubic) {
+            if (s->use_texture) { g_error = "PHOTON_INTERPOLATION=cubic is not available with PHOTON_SAMPLER=texture"; return false; }
+            if (!ensure_coefficients(*s->field, s->stream)) return false;
+            // the spline of a constant region reproduces it to rounding only: keep the "below the global
+            // minimum" fallback (trace.h:1056) from firing on the last bit
+            a.field.data_min = a.field.data_min - 1e-4f * fabsf(a.field.data_min);
+            a.field.skip_step = a.field.step / (1 + a.field.data_min);
+        }
     }
 
     // ---- image + counters
@@ -582,6 +617,59 @@ int photon_b200_load_field(const char *path, float meta16[16], float *out, long 
         if (out && capacity_voxels >= (long long)n)
             rc = cudaMemcpy(out, F->lin, n * sizeof(f4), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
     }
+    cudaStreamDestroy(st);
+    return rc;
+}
+
+int photon_b200_load_coefficients(const char *path, float *out, long long capacity_voxels) {
+    g_error.clear();
+    if (photon_b200_device_count() < 1) { g_error = "no CUDA device available"; return 1; }
+    int dev = pick_device(-1);
+    if (cudaSetDevice(dev) != cudaSuccess) return 1;
+    cudaStream_t st;
+    if (cudaStreamCreate(&st) != cudaSuccess) return 1;
+    DeviceField *F = get_field(path, dev, st);
+    int rc = 1;
+    if (F && ensure_coefficients(*F, st)) {
+        size_t n = (size_t)F->P.W * F->P.H * F->P.D;
+        rc = 0;
+        if (out && capacity_voxels >= (long long)n)
+            rc = cudaMemcpy(out, F->coef, n * sizeof(float), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
+    }
+    cudaStreamDestroy(st);
+    return rc;
+}
+
+int photon_b200_sample_field(const char *path, int cubic, int n, const float *xyz_texel, float *out4) {
+    g_error.clear();
+    if (photon_b200_device_count() < 1) { g_error = "no CUDA device available"; return 1; }
+    if (n <= 0) return 0;
+    int dev = pick_device(-1);
+    if (cudaSetDevice(dev) != cudaSuccess) return 1;
+    cudaStream_t st;
+    if (cudaStreamCreate(&st) != cudaSuccess) return 1;
+    DeviceField *F = get_field(path, dev, st);
+    int rc = 1;
+    float *d_in = nullptr, *d_out = nullptr;
+    if (F && (!cubic || ensure_coefficients(*F, st)) &&
+        cudaMalloc(&d_in, (size_t)n * 3 * sizeof(float)) == cudaSuccess &&
+        cudaMalloc(&d_out, (size_t)n * 4 * sizeof(float)) == cudaSuccess &&
+        cudaMemcpyAsync(d_in, xyz_texel, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, st) == cudaSuccess) {
+        int blocks = (n + 127) / 128;
+        if (cubic) {
+            BSplineField S; S.c = F->coef; S.W = F->P.W; S.H = F->P.H; S.D = F->P.D;
+            S.inv_sp = mk3(1.0f / F->spacing.x, 1.0f / F->spacing.y, 1.0f / F->spacing.z);
+            sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
+        } else {
+            LinearField S; S.g = F->lin; S.W = F->P.W; S.H = F->P.H; S.D = F->P.D;
+            sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
+        }
+        if (cudaGetLastError() == cudaSuccess &&
+            cudaMemcpyAsync(out4, d_out, (size_t)n * 4 * sizeof(float), cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+            cudaStreamSynchronize(st) == cudaSuccess) rc = 0;
+    }
+    if (rc) { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && g_error.empty()) g_error = cudaGetErrorString(e); }
+    cudaFree(d_in); cudaFree(d_out);
     cudaStreamDestroy(st);
     return rc;
 }

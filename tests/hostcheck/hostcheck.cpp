@@ -6,6 +6,7 @@
 // tile / warp aggregation is NOT exercised here (that needs the GPU tests).
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -44,7 +45,11 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
     a.mie.angle = sc->scattering_angle; a.mie.irradiance = sc->scattering_irradiance;
     a.aim = aim.data();
     std::vector<f4> field;
-    LinearField S{}; 
+    std::vector<float> coef;
+    LinearField S{};
+    BSplineField SC{};
+    const char *ip = getenv("PHOTON_INTERPOLATION");
+    const bool cubic = simulate_density_gradients && ip && strcmp(ip, "cubic") == 0;
     a.simulate_gradients = simulate_density_gradients;
     if (simulate_density_gradients) {
         pnrrd::Volume vol;
@@ -70,8 +75,20 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
             if (o.w < dmin) dmin = o.w;
         }
         P.data_min = dmin; P.skip_step = P.step / (1 + P.data_min);
-        a.field = P;
         S.g = field.data(); S.W = sx; S.H = sy; S.D = sz;
+        if (cubic) {                                 // same ingest as driver.cu ensure_coefficients
+            size_t W = sx, H = sy, D = sz;
+            coef.resize(W * H * D);
+            for (size_t i = 0; i < coef.size(); i++) coef[i] = field[i].w;
+            for (size_t l = 0; l < H * D; l++) prefilter_line(&coef[l * W], W, 1);
+            for (size_t l = 0; l < W * D; l++) prefilter_line(&coef[(l / W) * W * H + (l % W)], H, W);
+            for (size_t l = 0; l < W * H; l++) prefilter_line(&coef[l], D, W * H);
+            SC.c = coef.data(); SC.W = sx; SC.H = sy; SC.D = sz;
+            SC.inv_sp = mk3(1.0f / (float)dx, 1.0f / (float)dy, 1.0f / (float)dz);
+            P.data_min = P.data_min - 1e-4f * fabsf(P.data_min);
+            P.skip_step = P.step / (1 + P.data_min);
+        }
+        a.field = P;
     }
     const int np = src->num_particles, nx = a.cam.nx, ny = a.cam.ny;
     std::vector<double> acc((size_t)nx * ny, 0.0);
@@ -94,7 +111,8 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
             for (int lr = 0; lr < rpp; lr++) {
                 long long gid = (long long)lr + (long long)(p - begin) * rpp;
                 bool save = dumps && gid < num_lightrays_save;
-                SensorSample s = trace_one<true>(a, S, p, lr, gid, save, steps);
+                SensorSample s = cubic ? trace_one<true>(a, SC, p, lr, gid, save, steps)
+                                       : trace_one<true>(a, S, p, lr, gid, save, steps);
                 if (!s.valid) continue;
                 if (erf_model) {
                     ErfFootprint fp; erf_footprint(fp, s.d_x, s.d_y, s.radiance, s.c4, a.cam.diffraction_diameter, erf_frac);

@@ -1,0 +1,156 @@
+"""Cubic mode (PHOTON_INTERPOLATION=cubic): tricubic B-spline interpolation of n-1 with analytic
+gradient on a scalar coefficient volume.  The reference's own cubic branch is unreachable through the
+ABI (prt.cu:3330 hard-codes interpolation_scheme = 1), so there is no reference output: PARITY
+UNPINNED.  What is checked instead:
+  CPU  the oracle's restatement of CubicInterpolationCUDA's published algorithm has the properties the
+       algorithm promises (knot reproduction, exactness on polynomials up to degree 3 away from the
+       faces, gradient = derivative of the value), agrees with the linear mode to O(h^2) on a smooth
+       field, and the product's stage code compiled for the host is bit-exact against it;
+  GPU  the CUDA prefilter is bit-exact against the oracle's, single samples agree to rounding, and
+       whole traces meet the north-star tolerances against the oracle in the same mode.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from photon_b200 import nrrd, scenes
+from tests import util
+
+
+@pytest.fixture()
+def cubic_env():
+    os.environ["PHOTON_INTERPOLATION"] = "cubic"
+    yield
+    os.environ.pop("PHOTON_INTERPOLATION", None)
+
+
+def oracle_samples(lib, path, cubic, pts):
+    pts = np.ascontiguousarray(pts, np.float32)
+    out = np.zeros((len(pts), 4), np.float32)
+    lib.photon_oracle_sample_field.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    assert lib.photon_oracle_sample_field(path.encode(), int(cubic), len(pts), pts.ctypes.data, out.ctypes.data) == 0
+    return out
+
+
+def oracle_coefficients(lib, path, shape):
+    out = np.zeros(shape, np.float32)
+    lib.photon_oracle_load_coefficients.argtypes = [C.c_char_p, C.c_void_p, C.c_longlong]
+    assert lib.photon_oracle_load_coefficients(path.encode(), out.ctypes.data, out.size) == 0
+    return out
+
+
+K = np.float32(0.225e-3)
+
+
+def write_field(path, rho, spacing=100.0):
+    n = rho.shape[0]
+    nrrd.write_nrrd(path, rho.astype(np.float32), (spacing,) * 3, (0.0, 0.0, 750e3))
+    return n
+
+
+def test_knot_reproduction_and_prefilter_inverse(oracle_lib, tmp_path):
+    """The spline through the prefiltered coefficients interpolates the samples (CI's defining property)."""
+    rng = np.random.default_rng(7)
+    n = 24
+    rho = 1.2 + 0.3 * rng.random((n, n, n))
+    path = str(tmp_path / "rand.nrrd")
+    write_field(path, rho)
+    kk, jj, ii = np.meshgrid(np.arange(2, n - 2), np.arange(2, n - 2), np.arange(2, n - 2), indexing="ij")
+    pts = np.stack([ii.ravel() + 0.5, jj.ravel() + 0.5, kk.ravel() + 0.5], axis=1)      # texel centres
+    got = oracle_samples(oracle_lib, path, 1, pts)[:, 3]
+    want = (K * rho.astype(np.float32))[kk.ravel(), jj.ravel(), ii.ravel()]
+    assert np.max(np.abs(got - want)) <= 2e-6 * np.max(np.abs(want))
+
+
+def test_exact_on_cubic_polynomial_with_analytic_gradient(oracle_lib, tmp_path):
+    n, h = 32, 100.0
+    c = np.arange(n, dtype=np.float64)
+    z, y, x = np.meshgrid(c, c, c, indexing="ij")
+    f = lambda x, y, z: 1.0 + 0.02 * x + 0.01 * y * z / n + 1e-3 * x * x - 2e-5 * x * x * x + 3e-4 * y * y + 1e-5 * z ** 3
+    path = str(tmp_path / "poly.nrrd")
+    write_field(path, f(x, y, z), h)
+    rng = np.random.default_rng(3)
+    p = rng.uniform(8.0, n - 9.0, (2000, 3))                 # grid units, away from the clamped faces
+    got = oracle_samples(oracle_lib, path, 1, p + 0.5)
+    px, py, pz = p[:, 0], p[:, 1], p[:, 2]
+    val = K * f(px, py, pz)
+    gx = K * (0.02 + 2e-3 * px - 6e-5 * px * px) / h
+    gy = K * (0.01 * pz / n + 6e-4 * py) / h
+    gz = K * (0.01 * py / n + 3e-5 * pz * pz) / h
+    scale = np.max(np.abs(val))
+    assert np.max(np.abs(got[:, 3] - val)) <= 5e-6 * scale
+    for g, w in ((got[:, 0], gx), (got[:, 1], gy), (got[:, 2], gz)):
+        assert np.max(np.abs(g - w)) <= 2e-4 * np.max(np.abs(w))
+
+
+def test_cubic_agrees_with_linear_on_a_smooth_field(oracle_lib, tmp_path):
+    path = str(tmp_path / "blob.nrrd")
+    n = 64
+    spacing = 511 * 176.0 / (n - 1)
+    nrrd.write_nrrd(path, scenes.gaussian_blob(n, spacing, 15e3), (spacing,) * 3, (0.0, 0.0, 750e3))
+    rng = np.random.default_rng(5)
+    p = rng.uniform(4.0, n - 4.0, (4000, 3)).astype(np.float32)
+    lin = oracle_samples(oracle_lib, path, 0, p)
+    cub = oracle_samples(oracle_lib, path, 1, p)
+    assert np.max(np.abs(lin[:, 3] - cub[:, 3])) <= 5e-3 * np.max(np.abs(lin[:, 3] - lin[:, 3].min()))     # linear is O(h^2)
+    g = np.max(np.abs(lin[:, :3]))
+    assert np.max(np.abs(lin[:, :3] - cub[:, :3])) <= 0.03 * g                           # O(h^2) on 64^3
+
+
+@pytest.mark.parametrize("alg", [2, 1])
+def test_stage_code_bit_exact_vs_oracle_cubic(alg, cubic_env, hostcheck_lib, oracle_lib, tmp_path):
+    c = scenes.c3_bos(str(tmp_path / "b.nrrd"), n=48, dots_per_side=8, points_per_dot=8, rays_per_point=16, algorithm=alg)
+    (tmp_path / "o").mkdir(); (tmp_path / "h").mkdir()
+    ref = util.run_with_dumps(oracle_lib, c, str(tmp_path / "o"))
+    got = util.run_with_dumps(hostcheck_lib, c, str(tmp_path / "h"))
+    assert np.array_equal(ref[1], got[1], equal_nan=True)
+    assert np.array_equal(ref[2], got[2], equal_nan=True)
+    os.environ.pop("PHOTON_INTERPOLATION")
+    (tmp_path / "l").mkdir()
+    lin = util.run_with_dumps(oracle_lib, c, str(tmp_path / "l"))
+    m = util.compare(lin, ref, 10.0)
+    assert 0 < m["dpos_px"] < 0.05, m                                                   # a different interpolant, same physics
+
+
+# ------------------------------------------------------------------------------------- GPU
+def cuda_samples(lib, path, cubic, pts):
+    pts = np.ascontiguousarray(pts, np.float32)
+    out = np.zeros((len(pts), 4), np.float32)
+    lib.photon_b200_sample_field.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    assert lib.photon_b200_sample_field(path.encode(), int(cubic), len(pts), pts.ctypes.data, out.ctypes.data) == 0
+    return out
+
+
+@pytest.mark.gpu
+def test_cuda_prefilter_bit_exact_and_samples(cuda_lib, oracle_lib, tmp_path):
+    path = str(tmp_path / "blob.nrrd")
+    n = 64
+    spacing = 511 * 176.0 / (n - 1)
+    rng = np.random.default_rng(11)
+    rho = scenes.gaussian_blob(n, spacing, 15e3) + 0.01 * rng.random((n, n, n)).astype(np.float32)
+    nrrd.write_nrrd(path, rho, (spacing,) * 3, (0.0, 0.0, 750e3))
+    want = oracle_coefficients(oracle_lib, path, (n, n, n))
+    got = np.zeros((n, n, n), np.float32)
+    cuda_lib.photon_b200_load_coefficients.argtypes = [C.c_char_p, C.c_void_p, C.c_longlong]
+    assert cuda_lib.photon_b200_load_coefficients(path.encode(), got.ctypes.data, got.size) == 0
+    assert np.array_equal(want, got)                                                     # same recursion, no contraction
+    p = rng.uniform(-0.5, n + 0.5, (20000, 3)).astype(np.float32)                        # includes the clamped faces
+    for cubic in (0, 1):
+        a = oracle_samples(oracle_lib, path, cubic, p)
+        b = cuda_samples(cuda_lib, path, cubic, p)
+        assert np.max(np.abs(a[:, 3] - b[:, 3])) <= 1e-6 * np.max(np.abs(a[:, 3]))
+        assert np.max(np.abs(a[:, :3] - b[:, :3])) <= 2e-5 * np.max(np.abs(a[:, :3]))    # FMA vs separate roundings
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("alg", [2, 1])
+def test_cuda_matches_oracle_cubic(alg, cubic_env, cuda_lib, oracle_lib, tmp_path):
+    c = scenes.c3_bos(str(tmp_path / "b.nrrd"), n=64, dots_per_side=10, points_per_dot=10, rays_per_point=20, algorithm=alg)
+    (tmp_path / "o").mkdir(); (tmp_path / "g").mkdir()
+    ref = util.run_with_dumps(oracle_lib, c, str(tmp_path / "o"))
+    got = util.run_with_dumps(cuda_lib, c, str(tmp_path / "g"))
+    m = util.compare(ref, got, 10.0)
+    print("cubic alg", alg, m)
+    util.assert_parity("bos_cubic", m)
