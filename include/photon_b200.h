@@ -99,6 +99,26 @@ float     photon_scene_last_trace_ms(photon_scene *s);  /* CUDA-event time of th
 int       photon_scene_kernel_launches(photon_scene *s);/* kernels launched by the last trace */
 int       photon_scene_num_points(photon_scene *s);     /* source points in this shard */
 
+/*
+ * Dot statistics: the on-device form of the reference's ray-dump consumer
+ * (python_codes/light_ray_processing.py:74-141 load_light_ray_positions/_directions,
+ * :211-237 calculate_lightray_deflections, :239-275 calculate_dot_average).  The reference writes
+ * 24 bytes per ray to pos_%04d.bin / dir_%04d.bin (prt.cu:3561-3611), reads them back with numpy,
+ * takes arccos of the direction cosines and sums segments of num_rays_per_dot consecutive rays.
+ * Here the same sums are accumulated during the trace, per segment of rays_per_dot consecutive rays
+ * of this scene (ray id = point * rays_per_point + ray, the dump order):
+ *   stats[dot*8 + 0..2]  sum of sensor positions x, y, z (um)
+ *   stats[dot*8 + 3..5]  sum of arccos(direction cosine) x, y, z after the volume (rad)
+ *   stats[dot*8 + 6]     rays that have a sensor position (the dump holds NaN for the others)
+ *   stats[dot*8 + 7]     rays that have a direction
+ * Enabled per scene; every later photon_scene_trace* adds to the sums until they are reset.
+ * Not available together with ray dumps, PHOTON_DETERMINISTIC or PHOTON_SAMPLER=texture.
+ */
+int       photon_scene_enable_dot_stats(photon_scene *s, long long rays_per_dot);
+long long photon_scene_num_dots(photon_scene *s);
+int       photon_scene_reset_dot_stats(photon_scene *s);
+int       photon_scene_download_dot_stats(photon_scene *s, double *host_stats, long long capacity_dots);
+
 /* Field ingest alone (replaces trace.h:1663-2105): loads the NRRD, builds (grad n, n-1) on
  * the GPU and copies it back.  meta16 = {min xyz, max xyz, spacing xyz, step, data_min, W, H, D, 0, 0}.
  * out may be NULL to query the size. */

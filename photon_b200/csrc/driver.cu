@@ -244,6 +244,8 @@ struct photon_scene {
     int last_launches = 0, total_launches = 0;
     int grid_blocks = 0;
     int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
+    double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
+    long long n_dots = 0, rays_per_dot = 0;
 };
 
 namespace {
@@ -265,12 +267,17 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     a.inter_pos = ipos; a.inter_dir = idir; a.n_inter = n_inter;
     const bool dump = fpos != nullptr || ipos != nullptr;
     int grid = std::min(point_count, s->grid_blocks);
+    a.dot_stats = s->d_dots; a.rays_per_dot = s->rays_per_dot; a.n_dots = s->n_dots;
+    const bool stats = s->d_dots != nullptr;
+    if (stats && (dump || s->d_fixed || s->use_texture)) {
+        g_error = "dot statistics are not available together with ray dumps, PHOTON_DETERMINISTIC or PHOTON_SAMPLER=texture"; return false; }
     if (s->use_texture && s->d_fixed) { g_error = "PHOTON_DETERMINISTIC is not available with PHOTON_SAMPLER=texture"; return false; }
     if (s->use_cubic && s->d_fixed) { g_error = "PHOTON_DETERMINISTIC is not available with PHOTON_INTERPOLATION=cubic"; return false; }
     if (s->use_cubic) {
         BSplineField S; S.c = s->field->coef; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         S.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
-        if (dump) trace_rays_kernel<true, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        if (stats) trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (dump) trace_rays_kernel<true, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     } else if (s->use_texture) {
         TextureField S; S.tex = s->field->tex;
@@ -279,7 +286,8 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     } else {
         LinearField S; S.g = s->field ? s->field->lin : nullptr;
         S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
-        if (s->d_fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (s->d_fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->d_fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->occupancy == 5) trace_rays_kernel<false, 5, LinearField, false, 128><<<grid, 128, 0, s->stream>>>(a, S);   // 96 regs, 20 warps/SM
@@ -462,7 +470,7 @@ void photon_scene_destroy(photon_scene *s) {
     cudaStream_t st = s->stream;
     pool_free(s->d_sx, st); pool_free(s->d_sy, st); pool_free(s->d_sz, st); pool_free(s->d_srad, st); pool_free(s->d_sdiam, st);
     pool_free(s->d_angle, st); pool_free(s->d_irr, st); pool_free(s->d_aim, st); pool_free(s->d_image, st); pool_free(s->d_counters, st);
-    pool_free(s->d_fixed, st);
+    pool_free(s->d_fixed, st); pool_free(s->d_dots, st);
     if (st) cudaStreamSynchronize(st);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -590,6 +598,30 @@ int photon_scene_reset_counters(photon_scene *s) {
     if (!scene_ok(s)) return 1;
     s->rays_traced = 0; s->total_launches = 0;
     return cuda_ok(cudaMemsetAsync(s->d_counters, 0, 2 * sizeof(unsigned long long), s->stream), "reset", __FILE__, __LINE__) ? 0 : 1;
+}
+// ---- dot statistics (light_ray_processing.py:211-275 on the device; include/photon_b200.h) ----
+int photon_scene_enable_dot_stats(photon_scene *s, long long rays_per_dot) {
+    if (!scene_ok(s)) return 1;
+    if (rays_per_dot < 1) { g_error = "rays_per_dot must be >= 1"; return 1; }
+    const long long rays = (long long)s->npoints * s->args.rpp;
+    const long long n = (rays + rays_per_dot - 1) / rays_per_dot;
+    if (s->d_dots) { pool_free(s->d_dots, s->stream); s->d_dots = nullptr; }
+    if (!pool_alloc(s->d_dots, (size_t)n * 8 * sizeof(double), s->stream)) return 1;
+    s->n_dots = n; s->rays_per_dot = rays_per_dot;
+    return cuda_ok(cudaMemsetAsync(s->d_dots, 0, (size_t)n * 8 * sizeof(double), s->stream), "dot stats", __FILE__, __LINE__) ? 0 : 1;
+}
+long long photon_scene_num_dots(photon_scene *s) { return s ? s->n_dots : -1; }
+int photon_scene_reset_dot_stats(photon_scene *s) {
+    if (!scene_ok(s)) return 1;
+    if (!s->d_dots) { g_error = "dot statistics are not enabled"; return 1; }
+    return cuda_ok(cudaMemsetAsync(s->d_dots, 0, (size_t)s->n_dots * 8 * sizeof(double), s->stream), "dot stats", __FILE__, __LINE__) ? 0 : 1;
+}
+int photon_scene_download_dot_stats(photon_scene *s, double *host, long long capacity_dots) {
+    if (!scene_ok(s)) return 1;
+    if (!s->d_dots) { g_error = "dot statistics are not enabled"; return 1; }
+    if (capacity_dots < s->n_dots) { g_error = "dot statistics buffer too small"; return 1; }
+    if (!cuda_ok(cudaMemcpyAsync(host, s->d_dots, (size_t)s->n_dots * 8 * sizeof(double), cudaMemcpyDeviceToHost, s->stream), "dot stats", __FILE__, __LINE__)) return 1;
+    return cuda_ok(cudaStreamSynchronize(s->stream), "dot stats", __FILE__, __LINE__) ? 0 : 1;
 }
 long long photon_scene_ray_steps(photon_scene *s) { return fetch_counters(s) ? (long long)s->h_counters[0] : -1; }
 long long photon_scene_sensor_hits(photon_scene *s) { return fetch_counters(s) ? (long long)s->h_counters[1] : -1; }

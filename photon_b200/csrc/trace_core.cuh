@@ -48,6 +48,11 @@ struct TraceArgs {
     f3 *inter_pos, *inter_dir;           // [n_save][n_inter] or null
     int n_inter;
     unsigned long long *counters;        // [0] committed ray-steps, [1] rays that reached the sensor
+    // dot statistics (the on-device form of light_ray_processing.py:211-275): per segment of rays_per_dot
+    // consecutive rays, [0..2] sum of sensor positions, [3..5] sum of arccos(direction after the volume),
+    // [6] rays with a sensor position, [7] rays with a direction.  null = off.
+    double *dot_stats;
+    long long rays_per_dot, n_dots;
 };
 
 // Result of tracing one ray up to the sensor plane
@@ -55,12 +60,14 @@ struct SensorSample {
     float d_x, d_y;
     double radiance, c4;
     bool valid;
+    f3 sdir, spos;                       // STATS only: what the ray dumps would hold (prt.cu:2136-2141, 2236-2240)
+    int sflags;                          // bit 0: sdir set, bit 1: spos set
 };
 
-template <bool DUMP, class Sampler>
+template <bool DUMP, class Sampler, bool STATS = false>
 PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr,
                                                   long long gid, bool save, unsigned long long &steps) {
-    SensorSample out; out.valid = false; out.d_x = out.d_y = 0; out.radiance = 0; out.c4 = 0;
+    SensorSample out; out.valid = false; out.d_x = out.d_y = 0; out.radiance = 0; out.c4 = 0; out.sflags = 0;
     float x_lens, y_lens;
     unsigned long long ray_index = (unsigned long long)(p + a.global_point_offset) * (unsigned long long)a.rpp + (unsigned long long)lr;
     if (a.rpp == 1) { x_lens = 0.0f; y_lens = 0.0f; }
@@ -90,6 +97,7 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
         if (any_nan(ray.dir) || any_nan(ray.pos)) return out;
     }
     if (DUMP && save) a.final_dir[gid] = ray.dir;                                // prt.cu:2136-2141
+    if (STATS) { out.sdir = ray.dir; out.sflags |= 1; }
     bool flip = true;
     f3 hit;
     if (a.train.e[0].type == 'n') {                                      // prt.cu:1545-1733
@@ -114,6 +122,7 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
     bool on = pixel_coords(hit, a.cam, flip, out.d_x, out.d_y);
     if (!on || is_nan(hit.x) || is_nan(hit.y)) return out;               // dump stays NaN (prt.cu:1449-1455, 2196)
     if (DUMP && save) a.final_pos[gid] = hit;
+    if (STATS) { out.spos = hit; out.sflags |= 2; }
     out.radiance = ray.radiance;
     out.c4 = cos4_alpha(ray.dir);
     out.valid = true;

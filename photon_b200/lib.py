@@ -62,6 +62,14 @@ def load_library(require_gpu=False):
         lib.photon_b200_load_field.restype = C.c_int
         lib.photon_scene_trace_range.argtypes = [C.c_void_p, C.c_int, C.c_int]
         lib.photon_scene_trace_range.restype = C.c_int
+        lib.photon_scene_enable_dot_stats.argtypes = [C.c_void_p, C.c_longlong]
+        lib.photon_scene_enable_dot_stats.restype = C.c_int
+        lib.photon_scene_num_dots.argtypes = [C.c_void_p]
+        lib.photon_scene_num_dots.restype = C.c_longlong
+        lib.photon_scene_reset_dot_stats.argtypes = [C.c_void_p]
+        lib.photon_scene_reset_dot_stats.restype = C.c_int
+        lib.photon_scene_download_dot_stats.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong]
+        lib.photon_scene_download_dot_stats.restype = C.c_int
         lib.photon_b200_measure_fp32_tflops.argtypes = [C.c_int]
         lib.photon_b200_measure_fp32_tflops.restype = C.c_double
         lib.photon_b200_measure_fp32x2_tflops.argtypes = [C.c_int]

@@ -95,6 +95,22 @@ class ResidentScene:
                                                    idr.ctypes.data if idr is not None else None), "trace_batch")
         return (pos, dr) if n_inter <= 0 else (pos, dr, ip, idr)
 
+    # dot statistics: light_ray_processing.py's dump consumer on the device (include/photon_b200.h)
+    def enable_dot_stats(self, rays_per_dot):
+        self._ck(self.lib.photon_scene_enable_dot_stats(self.handle, int(rays_per_dot)), "enable_dot_stats")
+        self._rays_per_dot = int(rays_per_dot)
+
+    def reset_dot_stats(self):
+        self._ck(self.lib.photon_scene_reset_dot_stats(self.handle), "reset_dot_stats")
+
+    def download_dot_stats(self):
+        """float64 [n_dots, 8]: sums of sensor x, y, z; sums of arccos(direction cosine) x, y, z; rays with a
+        position; rays with a direction."""
+        n = int(self.lib.photon_scene_num_dots(self.handle))
+        out = np.zeros((n, 8), np.float64)
+        self._ck(self.lib.photon_scene_download_dot_stats(self.handle, out.ctypes.data, n), "download_dot_stats")
+        return out
+
     def reset_counters(self):
         self._ck(self.lib.photon_scene_reset_counters(self.handle), "reset_counters")
 

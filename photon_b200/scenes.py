@@ -224,3 +224,62 @@ def c1_piv(*, particles=50000, rays_per_particle=10000, nx=1024, ny=1024, seed=1
         call.mie_beam = np.array([0, 1, 0], np.float32)
         call.mie_inverse_rotation = np.eye(3, dtype=np.float32).reshape(-1)
     return call
+
+
+def turbulent_field(n, *, seed=1, k_lo=4.0, k_hi=128.0, rms=0.05, rho0=1.225, device=None):
+    """Band-limited Gaussian random density field of BASELINE.md C4: white noise from
+    ``default_rng(seed)`` shaped in Fourier space to E(k) ~ k^-5/3 for k_lo <= |k| <= k_hi (cycles
+    per box), zero elsewhere, scaled to an rms of ``rms`` around ``rho0``.  float32 [z][y][x].
+    The FFT runs with numpy, or with torch on ``device`` (the 1024^3 case takes minutes on a CPU).
+    Amplitude per mode = sqrt(E(k) / (4 pi k^2)) ~ k^(-11/6)."""
+    rng = np.random.default_rng(seed)
+    w = rng.standard_normal((n, n, n), dtype=np.float32)
+    kz = np.fft.fftfreq(n, 1.0 / n).astype(np.float32)
+    kx = np.fft.rfftfreq(n, 1.0 / n).astype(np.float32)
+    if device is not None:
+        import torch
+        t = torch.from_numpy(w).to(device)
+        F = torch.fft.rfftn(t)
+        del t
+        kzt, kxt = torch.from_numpy(kz).to(device), torch.from_numpy(kx).to(device)
+        k = torch.sqrt(kzt[:, None, None] ** 2 + kzt[None, :, None] ** 2 + kxt[None, None, :] ** 2)
+        amp = torch.where((k >= k_lo) & (k <= k_hi), k.clamp(min=1.0) ** (-11.0 / 6.0), torch.zeros_like(k))
+        del k
+        F *= amp
+        del amp
+        f = torch.fft.irfftn(F, s=(n, n, n))
+        del F
+        f *= rms / f.std()
+        f += rho0
+        return f.to(torch.float32).cpu().numpy()
+    F = np.fft.rfftn(w)
+    k = np.sqrt(kz[:, None, None] ** 2 + kz[None, :, None] ** 2 + kx[None, None, :] ** 2)
+    amp = np.where((k >= k_lo) & (k <= k_hi), np.maximum(k, 1.0) ** (-11.0 / 6.0), 0.0)
+    f = np.fft.irfftn(F * amp, s=(n, n, n))
+    f *= rms / f.std()
+    return (f + rho0).astype(np.float32)
+
+
+def c4_piv(nrrd_path, *, n=1024, particles=1000000, rays_per_particle=1000, nx=2048, ny=2048,
+           write_field=True, seed=2, device=None, frame_shift_um=0.0, source_point_number=10000):
+    """PIV with Mie-scattering particles seen through a turbulent density field.
+
+    n^3 band-limited random field (:func:`turbulent_field`, k = 4..min(128, n/4)), extent 200 mm,
+    NRRD origin (-100 mm, -100 mm, 450 mm): volume-frame z in [-300, -100] mm, between the light sheet
+    (z = -50 mm for an object distance of 700 mm) and the lens.  Particles uniform in +-75 x +-75 x
+    +-7.5 mm (``default_rng(seed)``), Gaussian sheet radiance, Mie table, thick lens f = 105 mm f/8,
+    nx x ny sensor of 17 um pixels, bilinear splat, RK4.  ``frame_shift_um`` displaces the particles
+    along x for the second frame of the image pair."""
+    from .nrrd import write_nrrd
+    call = c1_piv(particles=particles, rays_per_particle=rays_per_particle, nx=nx, ny=ny, seed=seed)
+    call.x = (call.x + np.float32(frame_shift_um)).astype(np.float32)
+    extent = 200e3
+    spacing = extent / (n - 1)
+    if write_field:
+        rho = turbulent_field(n, seed=1, k_hi=min(128.0, n / 4.0), device=device)
+        write_nrrd(nrrd_path, rho, (spacing,) * 3, (-extent / 2, -extent / 2, 450e3))
+    call.source_point_number = source_point_number
+    call.simulate_density_gradients = True
+    call.density_grad_filename = str(nrrd_path)
+    call.ray_tracing_algorithm = 2
+    return call

@@ -7,6 +7,12 @@ from photon_b200 import scenes
 from photon_b200.scene import ResidentScene
 
 def make(name, d):
+    if name.startswith("c4"):                    # c4 or c4_<n>: BASELINE C4 (turbulent n^3 field, Mie, thick lens, 4 MP)
+        import torch
+        n = int(name.split("_")[1]) if "_" in name else 1024
+        nrrd = os.path.join(d, "probe_turb_%d.nrrd" % n)
+        return scenes.c4_piv(nrrd, n=n, particles=100000, rays_per_particle=1000, write_field=not os.path.exists(nrrd),
+                             device="cuda" if torch.cuda.is_available() else None)
     if name.startswith("piv"):
         c = scenes.c1_piv(particles=20000, rays_per_particle=10000)
         if name == "piv_diffraction":
@@ -37,6 +43,8 @@ for name in (sys.argv[1:] or ["piv", "piv_thin", "piv_diffuse", "piv_diffraction
         s.trace_range(0, n); ms.append(s.last_trace_ms)
     rays = n * call.lightray_number_per_particle
     img = s.download_image()
-    print("%-16s %8.2f ms  %.3e rays/s  steps/ray %.1f  hits %.3f  image sum %.4g" % (
-        name, np.mean(ms), rays / (np.mean(ms) * 1e-3), s.ray_steps / max(s.rays, 1), s.sensor_hits / max(s.rays, 1), img.sum()), flush=True)
+    spr = s.ray_steps / max(s.rays, 1)
+    print("%-16s %8.2f ms  %.3e rays/s  %.3e ray-steps/s  steps/ray %.1f  hits %.3f  image sum %.4g" % (
+        name, np.mean(ms), rays / (np.mean(ms) * 1e-3), rays * spr / (np.mean(ms) * 1e-3), spr,
+        s.sensor_hits / max(s.rays, 1), img.sum()), flush=True)
     s.close()
