@@ -119,6 +119,21 @@ long long photon_scene_num_dots(photon_scene *s);
 int       photon_scene_reset_dot_stats(photon_scene *s);
 int       photon_scene_download_dot_stats(photon_scene *s, double *host_stats, long long capacity_dots);
 
+/*
+ * Mie scattering table (host code, double precision).
+ * photon_b200_bhmie replaces python_codes/bhmie.py:3-173 (Bohren & Huffman): size parameter x, relative
+ * refractive index (re, im), nang angles in [0, 90] deg -> s1, s2 = 2*nang-1 complex amplitudes over
+ * [0, 180] deg (interleaved re, im) and q4 = {qext, qsca, qback, gsca} (q4 may be NULL).
+ * photon_b200_mie_irradiance_table replaces calculate_mie_scattering_intensity
+ * (run_simulation_02.py:641-696): for each particle size, x = 2 pi size n_medium / wavelength and
+ * irradiance[angle*num_sizes + size] = (|s1|^2 + |s2|^2) / 2 -- the row-major table scattering_data_t
+ * carries (prt.cu:196-198) -- with scattering_angle[2*nang-1] in radians.
+ */
+int photon_b200_bhmie(double x, double refrel_re, double refrel_im, int nang, double *s1, double *s2, double *q4);
+int photon_b200_mie_irradiance_table(const double *particle_sizes, int num_sizes, double medium_refractive_index,
+                                     double particle_refractive_index, double beam_wavelength, int nang,
+                                     double *scattering_angle, double *scattering_irradiance);
+
 /* Field ingest alone (replaces trace.h:1663-2105): loads the NRRD, builds (grad n, n-1) on
  * the GPU and copies it back.  meta16 = {min xyz, max xyz, spacing xyz, step, data_min, W, H, D, 0, 0}.
  * out may be NULL to query the size. */

@@ -22,6 +22,7 @@
 #include "nrrd_reader.h"
 #include "scene_args.h"
 #include "trace_kernel.cuh"
+#include "mie_table.h"
 
 using namespace ph;
 
@@ -310,6 +311,36 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
 extern "C" {
 
 int photon_b200_abi_version(void) { return 1; }
+
+// ---- Mie table (host; replaces bhmie.py and run_simulation_02.py:641-696) ----
+int photon_b200_bhmie(double x, double refrel_re, double refrel_im, int nang, double *s1, double *s2, double *q4) {
+    g_error.clear();
+    if (nang < 2 || !s1 || !s2) { g_error = "bhmie: nang must be >= 2 and the outputs non-null"; return 1; }
+    if (!(x > 0.0)) { g_error = "bhmie: size parameter must be positive"; return 1; }
+    if (ph::bhmie_host(x, refrel_re, refrel_im, nang, s1, s2, q4) != 0) { g_error = "bhmie: nang > 1000 or nmx > 150000"; return 1; }
+    return 0;
+}
+int photon_b200_mie_irradiance_table(const double *particle_sizes, int num_sizes, double medium_refractive_index,
+                                     double particle_refractive_index, double beam_wavelength, int nang,
+                                     double *scattering_angle, double *scattering_irradiance) {
+    g_error.clear();
+    if (nang < 2 || num_sizes < 1 || !particle_sizes || !scattering_angle || !scattering_irradiance) {
+        g_error = "mie table: bad arguments"; return 1; }
+    const int rows = 2 * nang - 1;
+    std::vector<double> s1(2 * rows), s2(2 * rows);
+    const double pi = 3.141592653589793;
+    for (int c = 0; c < num_sizes; c++) {
+        const double x = 2 * pi * particle_sizes[c] * medium_refractive_index / beam_wavelength;      // rs02.py:676
+        if (!(x > 0.0) || ph::bhmie_host(x, particle_refractive_index / medium_refractive_index, 0.0, nang, s1.data(), s2.data(), nullptr) != 0) {
+            g_error = "mie table: bhmie failed for size index " + std::to_string(c); return 1; }
+        for (int r = 0; r < rows; r++)                                                                // rs02.py:690-692
+            scattering_irradiance[(size_t)r * num_sizes + c] =
+                0.5 * ((s1[2 * r] * s1[2 * r] + s1[2 * r + 1] * s1[2 * r + 1]) + (s2[2 * r] * s2[2 * r] + s2[2 * r + 1] * s2[2 * r + 1]));
+    }
+    const double dang = 0.5 * pi / (nang - 1);
+    for (int r = 0; r < rows; r++) scattering_angle[r] = ((double)(r + 1) - 1.0) * dang;            // rs02.py:688
+    return 0;
+}
 
 int photon_b200_device_count(void) {
     int n = 0;

@@ -273,6 +273,13 @@ def c4_piv(nrrd_path, *, n=1024, particles=1000000, rays_per_particle=1000, nx=2
     from .nrrd import write_nrrd
     call = c1_piv(particles=particles, rays_per_particle=rays_per_particle, nx=nx, ny=ny, seed=seed)
     call.x = (call.x + np.float32(frame_shift_um)).astype(np.float32)
+    # the Bohren-Huffman table the reference builds for a PIV run (rs02.py:641-696): 27 diameters x 255 angles
+    from .mie import calculate_mie_scattering_intensity
+    ang, irr = calculate_mie_scattering_intensity(
+        {"particle_field": {"medium_refractive_index": 1.0, "particle_refractive_index": 1.46,
+                            "mie_scattering_angle_number": 128, "beam_wavelength": 0.532}}, np.linspace(0.1, 2.0, 27))
+    call.mie_angles, call.mie_irradiance = ang.astype(np.float32), np.ascontiguousarray(irr, np.float32)
+    call.diameter_index = np.random.default_rng(seed + 1).integers(0, 27, particles).astype(np.int32)
     extent = 200e3
     spacing = extent / (n - 1)
     if write_field:
