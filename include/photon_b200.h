@@ -66,7 +66,14 @@ void photon_scene_destroy(photon_scene *s);
 int   photon_scene_zero_image(photon_scene *s);
 int   photon_scene_upload_image(photon_scene *s, const float *host_image);      /* H2D */
 int   photon_scene_download_image(photon_scene *s, float *host_image);          /* D2H, overwrites */
-void *photon_scene_image_device_ptr(photon_scene *s);                           /* for NCCL reduce by the caller */
+void *photon_scene_image_device_ptr(photon_scene *s);
+/* The step after the path (perform_ray_tracing_03.py:2189-2243) on the device: optional N(0, image_noise*100)
+ * added to the raw image (Philox keyed by pixel and seed; the reference seeds numpy from the clock), negatives
+ * and non-finite values to 0, x 10^(pixel_gain/20), rescale by the maximum to 2^bit_depth-1 levels, round
+ * half-even, stretch to the 16-bit range, narrow to uint16 -- in float32 like numpy on the float32 image.
+ * host_out: ny*nx uint16 (half the D2H bytes of the raw image). */
+int   photon_scene_export_u16(photon_scene *s, float pixel_gain, int pixel_bit_depth, int intensity_rescaling,
+                              float image_noise, unsigned int seed, unsigned short *host_out);                           /* for NCCL reduce by the caller */
 /* Deterministic mode: 1 if the scene accumulates in fixed point; the raw int64 image (increments in
  * units of 1/scale, the same scale for every shard of a call) for an exact cross-GPU sum. */
 int   photon_scene_deterministic(photon_scene *s);
@@ -118,6 +125,29 @@ int       photon_scene_enable_dot_stats(photon_scene *s, long long rays_per_dot)
 long long photon_scene_num_dots(photon_scene *s);
 int       photon_scene_reset_dot_stats(photon_scene *s);
 int       photon_scene_download_dot_stats(photon_scene *s, double *host_stats, long long capacity_dots);
+
+/*
+ * Source-point generation, the step before the path (host code).  Replaces the Python loops of
+ * python_codes/run_simulation_02.py.  Random draws are INPUTS (the reference uses numpy's clock-seeded global
+ * generator): hand over numpy's own stream to reproduce a reference run, or any other stream.
+ *   photon_b200_sunflower            calculate_sunflower_coordinates (:999-1055); ring_phase_u = one draw per ring
+ *                                    or NULL for phase 0; x, y may be NULL to query the count (return value)
+ *   photon_b200_non_overlapping_dots create_non_overlapping_dot_coordinates (:1251-1326), hash grid instead of the
+ *                                    O(n^2) distance scan; uniforms = 2 per iteration; returns dots placed into xy[2*i]
+ *   photon_b200_expand_dots          the per-dot loop of generate_bos_lightfield_data (:1485-1530) into the
+ *                                    lightfield_source_t arrays (x, y, z float32; radiance float64; diameter_index 1)
+ *   photon_b200_piv_particles        load_lightfield_data (:941-975): uniform box, Gaussian sheet radiance, camera
+ *                                    rotation (row-major 3x3), shift to the object plane
+ */
+long long photon_b200_sunflower(double diameter, double count, const double *ring_phase_u, double *x, double *y, long long capacity);
+long long photon_b200_non_overlapping_dots(double xmin, double xmax, double ymin, double ymax, long long num_dots,
+                                           double dot_diameter, const double *uniforms, long long n_pairs, double *xy,
+                                           long long *iterations_used /* may be NULL */);
+int photon_b200_expand_dots(const double *dot_x, const double *dot_y, long long ndots, const double *off_x, const double *off_y,
+                            long long noff, double z, double radiance, float *x, float *y, float *zz, double *rad, int *diam);
+int photon_b200_piv_particles(long long n, const double *ux, const double *uy, const double *uz, const double lo[3],
+                              const double hi[3], double gaussian_beam_fwhm, double irradiance_constant, const double rotation[9],
+                              double z_object, float *x, float *y, float *z, double *rad, int *diam);
 
 /*
  * Mie scattering table (host code, double precision).

@@ -23,6 +23,7 @@
 #include "scene_args.h"
 #include "trace_kernel.cuh"
 #include "mie_table.h"
+#include "source_points.h"
 
 using namespace ph;
 
@@ -312,6 +313,35 @@ extern "C" {
 
 int photon_b200_abi_version(void) { return 1; }
 
+// ---- source-point generation (host; replaces the Python loops of run_simulation_02.py) ----
+long long photon_b200_sunflower(double diameter, double count, const double *ring_phase_u, double *x, double *y, long long capacity) {
+    g_error.clear();
+    if (!(diameter > 0.0) || !(count >= 1.0)) { g_error = "sunflower: diameter and count must be positive"; return -1; }
+    return ph::sunflower_points(diameter, count, ring_phase_u, x, y, (x && y) ? capacity : 0);
+}
+long long photon_b200_non_overlapping_dots(double xmin, double xmax, double ymin, double ymax, long long num_dots,
+                                           double dot_diameter, const double *uniforms, long long n_pairs, double *xy,
+                                           long long *iterations_used) {
+    g_error.clear();
+    if (!uniforms || !xy || num_dots < 0) { g_error = "non_overlapping_dots: bad arguments"; return -1; }
+    return ph::non_overlapping_dots(xmin, xmax, ymin, ymax, num_dots, dot_diameter, uniforms, n_pairs, 50000, xy, iterations_used);
+}
+int photon_b200_expand_dots(const double *dot_x, const double *dot_y, long long ndots, const double *off_x, const double *off_y,
+                            long long noff, double z, double radiance, float *x, float *y, float *zz, double *rad, int *diam) {
+    g_error.clear();
+    if (!dot_x || !dot_y || !off_x || !off_y || !x || !y || !zz || !rad || !diam) { g_error = "expand_dots: null argument"; return 1; }
+    ph::expand_dots(dot_x, dot_y, ndots, off_x, off_y, noff, z, radiance, x, y, zz, rad, diam);
+    return 0;
+}
+int photon_b200_piv_particles(long long n, const double *ux, const double *uy, const double *uz, const double lo[3],
+                              const double hi[3], double gaussian_beam_fwhm, double irradiance_constant, const double rotation[9],
+                              double z_object, float *x, float *y, float *z, double *rad, int *diam) {
+    g_error.clear();
+    if (!ux || !uy || !uz || !lo || !hi || !rotation || !x || !y || !z || !rad || !diam) { g_error = "piv_particles: null argument"; return 1; }
+    ph::piv_particles(n, ux, uy, uz, lo, hi, gaussian_beam_fwhm, irradiance_constant, rotation, z_object, x, y, z, rad, diam);
+    return 0;
+}
+
 // ---- Mie table (host; replaces bhmie.py and run_simulation_02.py:641-696) ----
 int photon_b200_bhmie(double x, double refrel_re, double refrel_im, int nang, double *s1, double *s2, double *q4) {
     g_error.clear();
@@ -551,6 +581,33 @@ int photon_scene_download_image(photon_scene *s, float *h) {
     if (!cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__)) return 1;
     if (stage) memcpy(h, stage, bytes);
     return 0;
+}
+int photon_scene_export_u16(photon_scene *s, float pixel_gain, int pixel_bit_depth, int intensity_rescaling,
+                            float image_noise, unsigned int seed, unsigned short *host_out) {
+    if (!scene_ok(s)) return 1;
+    if (!host_out || pixel_bit_depth < 1 || pixel_bit_depth > 16) { g_error = "export_u16: bad arguments"; return 1; }
+    if (!fold_fixed(s)) return 1;
+    const size_t n = (size_t)s->args.cam.nx * s->args.cam.ny;
+    float *tmp = nullptr; unsigned short *d16 = nullptr; unsigned int *dmax = nullptr;
+    bool ok = pool_alloc(tmp, n * sizeof(float), s->stream) && pool_alloc(d16, n * sizeof(unsigned short), s->stream) &&
+              pool_alloc(dmax, sizeof(unsigned int), s->stream);
+    if (ok) {
+        const float gain = (float)std::pow(10.0, (double)pixel_gain / 20.0);
+        const float levels = (float)((1 << pixel_bit_depth) - 1);
+        const float k = (float)((65536.0 - 1.0) / ((double)(1 << pixel_bit_depth) - 1.0));
+        const unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8);
+        ok = cuda_ok(cudaMemsetAsync(dmax, 0, sizeof(unsigned int), s->stream), "export", __FILE__, __LINE__);
+        if (ok) {
+            export_prepare_kernel<<<blocks, 256, 0, s->stream>>>(s->d_image, tmp, n, gain, image_noise * 100.0f, seed,
+                                                                 intensity_rescaling, dmax);
+            export_u16_kernel<<<blocks, 256, 0, s->stream>>>(tmp, d16, n, levels, k, intensity_rescaling, dmax);
+            ok = cuda_ok(cudaGetLastError(), "export kernels", __FILE__, __LINE__) &&
+                 cuda_ok(cudaMemcpyAsync(host_out, d16, n * sizeof(unsigned short), cudaMemcpyDeviceToHost, s->stream), "export D2H", __FILE__, __LINE__) &&
+                 cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__);
+        }
+    }
+    pool_free(tmp, s->stream); pool_free(d16, s->stream); pool_free(dmax, s->stream);
+    return ok ? 0 : 1;
 }
 void *photon_scene_image_device_ptr(photon_scene *s) { return s ? (void *)s->d_image : nullptr; }
 

@@ -58,6 +58,17 @@ class ResidentScene:
         self._ck(self.lib.photon_scene_download_image(self.handle, out.ctypes.data), "download_image")
         return out
 
+    def export_u16(self, pixel_gain=None, pixel_bit_depth=None, intensity_rescaling=True, image_noise=0.0, seed=0):
+        """The 16-bit image the reference writes to TIFF (pr03.py:2189-2243), computed on the device.
+        Defaults for gain / bit depth come from the call's camera_design."""
+        cam = self.call.camera
+        g = cam.pixel_gain if pixel_gain is None else pixel_gain
+        b = cam.pixel_bit_depth if pixel_bit_depth is None else pixel_bit_depth
+        out = np.empty(self.shape, np.uint16)
+        self._ck(self.lib.photon_scene_export_u16(self.handle, float(g), int(b), int(bool(intensity_rescaling)),
+                                                  float(image_noise), int(seed) & 0xffffffff, out.ctypes.data), "export_u16")
+        return out
+
     @property
     def deterministic(self):
         return bool(self.lib.photon_scene_deterministic(self.handle))
