@@ -247,10 +247,40 @@ struct photon_scene {
     int grid_blocks = 0;
     int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
     double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
+    int *d_order = nullptr;              // processing order of the source points (Morton order of x, y), or null
     long long n_dots = 0, rays_per_dot = 0;
 };
 
 namespace {
+
+// Morton (Z-order) permutation of points by (x, y) quantised to 16 bits per axis over their bounding box:
+// 4-pass LSD radix sort of the 32-bit keys (stable, O(n)).
+inline uint32_t spread16(uint32_t v) {
+    v &= 0xffffu; v = (v | (v << 8)) & 0x00ff00ffu; v = (v | (v << 4)) & 0x0f0f0f0fu;
+    v = (v | (v << 2)) & 0x33333333u; v = (v | (v << 1)) & 0x55555555u;
+    return v;
+}
+std::vector<int> morton_order(const float *x, const float *y, size_t n) {
+    float x0 = x[0], x1 = x[0], y0 = y[0], y1 = y[0];
+    for (size_t i = 1; i < n; i++) { x0 = std::min(x0, x[i]); x1 = std::max(x1, x[i]); y0 = std::min(y0, y[i]); y1 = std::max(y1, y[i]); }
+    const float kx = x1 > x0 ? 65535.0f / (x1 - x0) : 0.0f, ky = y1 > y0 ? 65535.0f / (y1 - y0) : 0.0f;
+    std::vector<uint32_t> key(n), key2(n);
+    std::vector<int> idx(n), idx2(n);
+    for (size_t i = 0; i < n; i++) {
+        const uint32_t qx = (uint32_t)std::min(65535.0f, std::max(0.0f, (x[i] - x0) * kx));
+        const uint32_t qy = (uint32_t)std::min(65535.0f, std::max(0.0f, (y[i] - y0) * ky));
+        key[i] = spread16(qx) | (spread16(qy) << 1); idx[i] = (int)i;
+    }
+    for (int pass = 0; pass < 4; pass++) {
+        size_t cnt[257] = {0};
+        const int sh = pass * 8;
+        for (size_t i = 0; i < n; i++) cnt[((key[i] >> sh) & 0xffu) + 1]++;
+        for (int b = 0; b < 256; b++) cnt[b + 1] += cnt[b];
+        for (size_t i = 0; i < n; i++) { const size_t d = cnt[(key[i] >> sh) & 0xffu]++; key2[d] = key[i]; idx2[d] = idx[i]; }
+        key.swap(key2); idx.swap(idx2);
+    }
+    return idx;
+}
 
 int pick_device(int requested) {
     if (requested >= 0) return requested;
@@ -270,6 +300,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     const bool dump = fpos != nullptr || ipos != nullptr;
     int grid = std::min(point_count, s->grid_blocks);
     a.dot_stats = s->d_dots; a.rays_per_dot = s->rays_per_dot; a.n_dots = s->n_dots;
+    a.order = dump ? nullptr : s->d_order;
     const bool stats = s->d_dots != nullptr;
     if (stats && (dump || s->d_fixed || s->use_texture)) {
         g_error = "dot statistics are not available together with ray dumps, PHOTON_DETERMINISTIC or PHOTON_SAMPLER=texture"; return false; }
@@ -410,6 +441,18 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         !upload(s->d_sdiam, src->diameter_index + b, n, s->stream)) return false;
     a.sx = s->d_sx; a.sy = s->d_sy; a.sz = s->d_sz; a.sradiance = s->d_srad; a.sdiam = s->d_sdiam;
     a.rpp = rpp; a.global_point_offset = s->point_offset;
+    // Processing order (north-star (b): Morton-ordered rays): consecutive CTAs take source points that are
+    // neighbours in (x, y), so the field columns they march through share texels in L1/L2 whatever order the
+    // caller generated the points in (random PIV particles: +7 % on C4).  Ray ids, dumps and dot statistics keep
+    // the caller's order -- only the point a CTA picks changes -- and dump launches use the identity order.
+    {
+        const char *mo = getenv("PHOTON_MORTON");
+        const bool want = mo ? atoi(mo) != 0 : simulate_density_gradients;
+        if (want && n > 1) {
+            std::vector<int> order = morton_order(src->x + b, src->y + b, n);
+            if (!upload(s->d_order, order.data(), n, s->stream)) return false;
+        }
+    }
 
     // ---- Mie table : prt.cu:3192-3210
     a.mie.enabled = strcmp(scattering_type_str, "mie") == 0;
@@ -531,7 +574,7 @@ void photon_scene_destroy(photon_scene *s) {
     cudaStream_t st = s->stream;
     pool_free(s->d_sx, st); pool_free(s->d_sy, st); pool_free(s->d_sz, st); pool_free(s->d_srad, st); pool_free(s->d_sdiam, st);
     pool_free(s->d_angle, st); pool_free(s->d_irr, st); pool_free(s->d_aim, st); pool_free(s->d_image, st); pool_free(s->d_counters, st);
-    pool_free(s->d_fixed, st); pool_free(s->d_dots, st);
+    pool_free(s->d_fixed, st); pool_free(s->d_dots, st); pool_free(s->d_order, st);
     if (st) cudaStreamSynchronize(st);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);

@@ -30,6 +30,7 @@ struct TraceArgs {
     const double *sradiance;
     const int *sdiam;
     int point_begin, point_count, rpp;
+    const int *order;                    // processing order: CTA slot i traces point order[i] (null = i)
     int dump_point_base;                 // first point of the dump batch (batch-local ray ids)
     int global_point_offset;             // index of shard point 0 in the caller's arrays (RNG keys)
     // lens samples: table of aim points [rpp] (reference draws) or Philox per ray

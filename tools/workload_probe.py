@@ -11,8 +11,19 @@ def make(name, d):
         import torch
         n = int(name.split("_")[1]) if "_" in name else 1024
         nrrd = os.path.join(d, "probe_turb_%d.nrrd" % n)
-        return scenes.c4_piv(nrrd, n=n, particles=100000, rays_per_particle=1000, write_field=not os.path.exists(nrrd),
-                             device="cuda" if torch.cuda.is_available() else None)
+        c = scenes.c4_piv(nrrd, n=n, particles=100000, rays_per_particle=1000, write_field=not os.path.exists(nrrd),
+                          device="cuda" if torch.cuda.is_available() else None)
+        if name.endswith("morton"):              # c4_<n>_morton: source points in Morton order of (x, y)
+            def spread(v):
+                v = v.astype(np.uint64) & 0xffff
+                v = (v | (v << 8)) & 0x00ff00ff; v = (v | (v << 4)) & 0x0f0f0f0f
+                v = (v | (v << 2)) & 0x33333333; v = (v | (v << 1)) & 0x55555555
+                return v
+            qx = ((c.x - c.x.min()) / (np.ptp(c.x) + 1e-9) * 65535).astype(np.uint64)
+            qy = ((c.y - c.y.min()) / (np.ptp(c.y) + 1e-9) * 65535).astype(np.uint64)
+            o = np.argsort(spread(qx) | (spread(qy) << 1), kind="stable")
+            c.x, c.y, c.z, c.radiance, c.diameter_index = c.x[o], c.y[o], c.z[o], c.radiance[o], c.diameter_index[o]
+        return c
     if name.startswith("piv"):
         c = scenes.c1_piv(particles=20000, rays_per_particle=10000)
         if name == "piv_diffraction":
