@@ -180,7 +180,7 @@ def run_reference_arm(args):
                                        "time inside the tracing kernel launches; the per-call NRRD load + gradient precompute "
                                        "(about 10 s at 512^3, single-threaded in the reference) is excluded"},
             "e2e": {"value": v, "unit": "ray-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, call):
@@ -193,8 +193,32 @@ def workload_config(args, call):
             "l2_policy": "field (2 GiB at 512^3) is larger than the 126 MB L2; consecutive steps trace different batches"}
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """The driver reads ONE JSON line from stdout.  Libraries write there too (NCCL prints its version line on
+    stdout, the host-compiled reference prints progress): send file descriptor 1 to stderr for the whole run and
+    keep the real stdout for emit()."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_JSON_FD, data)
+
+
 def main():
     args = parse()
+    claim_stdout()
     if args.impl == "reference":
         return run_reference_arm(args)
 
@@ -341,7 +365,7 @@ def main():
                                     "kind": kind, "rays_per_s": r["rays"] / r["seconds"],
                                     "sample": f"first {n} source points x {args.rays_per_point} rays of the same workload "
                                               f"({r['rays']} rays, {r['steps']} ray-steps, {r['seconds']:.1f} s); field load excluded"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     scene.close()
     if world > 1:
         dist.destroy_process_group()
