@@ -248,6 +248,7 @@ struct photon_scene {
     int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
     double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
     int *d_order = nullptr;              // processing order of the source points (Morton order of x, y), or null
+    bool coherent = false;               // rays of a source point stay within ~a cell of each other: v5 hot loop
     long long n_dots = 0, rays_per_dot = 0;
 };
 
@@ -323,6 +324,10 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         else if (s->d_fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->d_fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (s->coherent && s->occupancy == 5) { LinearFieldCoherent C; static_cast<LinearField &>(C) = S;
+            trace_rays_kernel<false, 5, LinearFieldCoherent, false, 128><<<grid, 128, 0, s->stream>>>(a, C); }
+        else if (s->coherent && s->occupancy == 3) { LinearFieldCoherent C; static_cast<LinearField &>(C) = S;
+            trace_rays_kernel<false, 3, LinearFieldCoherent><<<grid, PH_BLOCK, 0, s->stream>>>(a, C); }
         else if (s->occupancy == 5) trace_rays_kernel<false, 5, LinearField, false, 128><<<grid, 128, 0, s->stream>>>(a, S);   // 96 regs, 20 warps/SM
         else if (s->occupancy == 6) trace_rays_kernel<false, 3, LinearField, false, 192><<<grid, 192, 0, s->stream>>>(a, S);   // 112 regs, 18 warps/SM
         else if (s->occupancy == 4) trace_rays_kernel<false, 4, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
@@ -484,6 +489,9 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         s->field = get_field(density_grad_filename, s->device, s->stream);
         if (!s->field) return false;
         a.field = s->field->P;
+        // coherent rays: the cone of a source point at the lens (cone_ratio * lens_pitch) is narrower than a cell
+        s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
+        if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;
         const char *smp = getenv("PHOTON_SAMPLER");
         s->use_texture = smp && strcmp(smp, "texture") == 0;
         if (s->use_texture && !ensure_texture(*s->field, s->stream)) return false;
