@@ -48,6 +48,8 @@ bool cuda_ok(cudaError_t e, const char *what, const char *file, int line) {
 // library twice per run and the reference reloads + recomputes the field each time).
 // ---------------------------------------------------------------------------------
 struct DeviceField {
+    int owner = -1;                      // the device this cache slot belongs to (never changes)
+    std::mutex mu;                       // builds of different devices run concurrently (PHOTON_GPUS)
     int device = -1;
     std::string path; long long mtime = 0, fsize = 0;
     FieldParams P{};
@@ -160,11 +162,15 @@ DeviceField *get_field(const char *path, int device, cudaStream_t st) {
     struct stat sb;
     long long mt = 0, fs = 0;
     if (stat(path, &sb) == 0) { mt = (long long)sb.st_mtim.tv_sec * 1000000000LL + sb.st_mtim.tv_nsec; fs = (long long)sb.st_size; }
-    std::lock_guard<std::mutex> lk(g_field_mutex);
     DeviceField *slot = nullptr;
-    for (auto *f : g_fields) if (f->device == device) slot = f;
-    if (slot && slot->path == path && slot->mtime == mt && slot->fsize == fs && !getenv("PHOTON_NO_FIELD_CACHE")) return slot;
-    if (slot) slot->release(); else { slot = new DeviceField(); g_fields.push_back(slot); }
+    {
+        std::lock_guard<std::mutex> lk(g_field_mutex);
+        for (auto *f : g_fields) if (f->owner == device) slot = f;
+        if (!slot) { slot = new DeviceField(); slot->owner = device; g_fields.push_back(slot); }
+    }
+    std::lock_guard<std::mutex> lk(slot->mu);
+    if (slot->device == device && slot->path == path && slot->mtime == mt && slot->fsize == fs && !getenv("PHOTON_NO_FIELD_CACHE")) return slot;
+    slot->release();
     if (!build_field(*slot, path, device, st)) { slot->release(); return nullptr; }
     slot->mtime = mt; slot->fsize = fs;
     return slot;
