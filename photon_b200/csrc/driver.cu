@@ -7,6 +7,7 @@
 // through one persistent launch unless ray dumps force the reference's per-batch files,
 // every CUDA call is checked, and nothing ever calls exit() inside the host process.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -24,6 +25,12 @@
 #include "trace_kernel.cuh"
 #include "mie_table.h"
 #include "source_points.h"
+#if defined(__has_include)
+#if __has_include(<nccl.h>)
+#include <nccl.h>
+#define PH_HAVE_NCCL 1
+#endif
+#endif
 
 using namespace ph;
 
@@ -872,7 +879,73 @@ bool write_f3_file(const std::string &dir, const char *prefix, int k, const floa
     return true;
 }
 
-struct ShardResult { bool ok = false; std::vector<float> image; std::vector<long long> fixed; double scale = 0; };
+struct ShardResult { bool ok = false; photon_scene *scene = nullptr; std::vector<float> image; std::vector<long long> fixed; double scale = 0; };
+
+// NCCL for the one exchange step the path has: the partial sensor images of a PHOTON_GPUS call are combined
+// with ONE ncclReduce over NVLink onto device 0.  The library is bound at run time (dlopen of
+// libnccl.so.2: no link-time dependency; without it the images are summed on the host, which is only a
+// different route for the same 4 MiB, not a compute fallback).  Communicators are created once per device
+// count with ncclCommInitAll and kept for the life of the process (no teardown at exit: the CUDA context may be
+// gone by then).
+#if PH_HAVE_NCCL
+struct NcclApi {
+    void *h = nullptr; bool tried = false;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    ncclResult_t (*Reduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    std::vector<ncclComm_t> comms; int ncomms = 0;
+    std::mutex mu;
+    bool load() {
+        if (tried) return h != nullptr;
+        tried = true;
+        if (const char *e = getenv("PHOTON_NCCL")) if (atoi(e) == 0) return false;
+        for (const char *name : {"libnccl.so.2", "libnccl.so"}) { h = dlopen(name, RTLD_NOW | RTLD_LOCAL); if (h) break; }
+        if (!h) return false;
+        CommInitAll = (decltype(CommInitAll))dlsym(h, "ncclCommInitAll");
+        GroupStart = (decltype(GroupStart))dlsym(h, "ncclGroupStart");
+        GroupEnd = (decltype(GroupEnd))dlsym(h, "ncclGroupEnd");
+        Reduce = (decltype(Reduce))dlsym(h, "ncclReduce");
+        GetErrorString = (decltype(GetErrorString))dlsym(h, "ncclGetErrorString");
+        if (!CommInitAll || !GroupStart || !GroupEnd || !Reduce) { dlclose(h); h = nullptr; }
+        return h != nullptr;
+    }
+    bool ensure(int n) {
+        if (!load()) return false;
+        if (ncomms == n) return true;
+        if (ncomms != 0) return false;                 // a different device count than the cached communicators
+        std::vector<int> devs(n); for (int i = 0; i < n; i++) devs[i] = i;
+        comms.resize(n);
+        ncclResult_t r = CommInitAll(comms.data(), n, devs.data());
+        if (r != ncclSuccess) { fprintf(stderr, "libparallel_ray_tracing(b200): ncclCommInitAll: %s; summing on the host\n", GetErrorString ? GetErrorString(r) : "?"); comms.clear(); return false; }
+        ncomms = n;
+        return true;
+    }
+};
+NcclApi g_nccl;
+// Sum the shard images onto scene 0 of device 0.  float mode: ncclFloat sum of the images; deterministic mode:
+// ncclUint64 sum of the fixed-point images (exact, order-free), folded into the float image once on device 0.
+bool nccl_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
+    std::lock_guard<std::mutex> lk(g_nccl.mu);
+    if (!g_nccl.ensure(n)) return false;
+    const bool fixed = res[0].scene->d_fixed != nullptr;
+    ncclResult_t r = g_nccl.GroupStart();
+    for (int g = 0; g < n && r == ncclSuccess; g++) {
+        photon_scene *s = res[g].scene;
+        cudaSetDevice(s->device);
+        if (fixed) r = g_nccl.Reduce(s->d_fixed, s->d_fixed, npix, ncclUint64, ncclSum, 0, g_nccl.comms[g], s->stream);
+        else r = g_nccl.Reduce(s->d_image, s->d_image, npix, ncclFloat, ncclSum, 0, g_nccl.comms[g], s->stream);
+    }
+    ncclResult_t e = g_nccl.GroupEnd();
+    if (r == ncclSuccess) r = e;
+    if (r != ncclSuccess) { fprintf(stderr, "libparallel_ray_tracing(b200): ncclReduce: %s\n", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"); return false; }
+    for (int g = 0; g < n; g++) { cudaSetDevice(res[g].scene->device); if (cudaStreamSynchronize(res[g].scene->stream) != cudaSuccess) return false; }
+    return true;
+}
+#else
+bool nccl_reduce_images(std::vector<ShardResult> &, int, size_t) { return false; }
+#endif
 
 }  // namespace
 
@@ -973,33 +1046,49 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
         th.emplace_back([&, g]() {
             photon_scene *s = make_scene(shard_index * ngpus + g, shard_count * ngpus, g);
             if (!s) return;
-            res[g].ok = photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
-            if (res[g].ok && photon_scene_deterministic(s)) {
-                res[g].fixed.resize(npix);
-                res[g].ok = photon_scene_download_image_fixed(s, res[g].fixed.data(), &res[g].scale) == 0;
-            } else if (res[g].ok) {
-                res[g].image.resize(npix);
-                res[g].ok = photon_scene_download_image(s, res[g].image.data()) == 0;
-            }
-            photon_scene_destroy(s);
+            res[g].scene = s;
+            res[g].ok = (g != 0 || photon_scene_upload_image(s, image_array) == 0)     // accumulate onto the caller's image
+                        && photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
         });
     }
     for (auto &t : th) t.join();
-    for (int g = 0; g < ngpus; g++) if (!res[g].ok) { fprintf(stderr, "libparallel_ray_tracing(b200): GPU %d failed; image untouched\n", g); return; }
-    if (!res[0].fixed.empty()) {          // deterministic: exact integer sum, one rounding (as on one GPU)
+    bool all_ok = true;
+    for (int g = 0; g < ngpus; g++) if (!res[g].ok) { fprintf(stderr, "libparallel_ray_tracing(b200): GPU %d failed; image untouched\n", g); all_ok = false; }
+    auto destroy_all = [&]() { for (int g = 0; g < ngpus; g++) if (res[g].scene) photon_scene_destroy(res[g].scene); };
+    if (!all_ok) { destroy_all(); return; }
+    lap("trace (all GPUs)");
+    if (nccl_reduce_images(res, ngpus, npix)) {                       // one reduce over NVLink, then one D2H
+        lap("nccl reduce");
+        photon_scene_download_image(res[0].scene, image_array);      // folds the fixed-point sum first, if any
+        lap("image D2H");
+        destroy_all();
+        return;
+    }
+    // no NCCL on this machine: the same sum through the host
+    const bool fixed = photon_scene_deterministic(res[0].scene) != 0;
+    for (int g = 0; g < ngpus && all_ok; g++) {
+        if (fixed) { res[g].fixed.resize(npix); all_ok = photon_scene_download_image_fixed(res[g].scene, res[g].fixed.data(), &res[g].scale) == 0; }
+        else if (g != 0) { res[g].image.resize(npix); all_ok = photon_scene_download_image(res[g].scene, res[g].image.data()) == 0; }
+    }
+    if (!all_ok) { fprintf(stderr, "libparallel_ray_tracing(b200): image download failed; image untouched\n"); destroy_all(); return; }
+    if (fixed) {                          // deterministic: exact integer sum, one rounding (as on one GPU)
         const double inv = 1.0 / res[0].scale;
         for (size_t i = 0; i < npix; i++) {
             long long q = 0;
             for (int g = 0; g < ngpus; g++) q += res[g].fixed[i];
             if (q != 0) image_array[i] += (float)((double)q * inv);
         }
-        return;
+    } else {
+        std::vector<float> img0(npix);
+        if (photon_scene_download_image(res[0].scene, img0.data()) == 0) {     // holds the caller's image + shard 0
+            for (size_t i = 0; i < npix; i++) {
+                float acc = img0[i];
+                for (int g = 1; g < ngpus; g++) acc += res[g].image[i];
+                image_array[i] = acc;
+            }
+        }
     }
-    for (size_t i = 0; i < npix; i++) {
-        float acc = image_array[i];
-        for (int g = 0; g < ngpus; g++) acc += res[g].image[i];
-        image_array[i] = acc;
-    }
+    destroy_all();
 }
 
 // ---------------------------------------------------------------------------------
