@@ -23,8 +23,15 @@
  *   PHOTON_GPUS=<n>         split the source points over n GPUs inside one call
  *   PHOTON_DETERMINISTIC=1  accumulate the image in 64-bit fixed point with integer atomics: the
  *                           result is bit-identical from run to run and for any sharding
- *   PHOTON_OCC=<2|3|4>      resident CTAs per SM the trace kernel variant is compiled for
+ *   PHOTON_OCC=<2..6>       resident CTAs per SM the trace kernel variant is compiled for
  *   PHOTON_TIMING=1         per-stage wall times of start_ray_tracing on stderr
+ *   PHOTON_INTERPOLATION=cubic  tricubic B-spline sampler on a prefiltered scalar volume (default: linear)
+ *   PHOTON_MORTON=<0|1>     CTAs take the source points in Morton order of (x, y) [default 1 with a density field]
+ *   PHOTON_HOT=<4|5>        RK4 hot loop: 5 = z-neighbour short path (coherent rays), 4 = without; default by the
+ *                           width of a source point's cone against the grid spacing
+ *   PHOTON_NCCL=0           PHOTON_GPUS: sum the partial images through the host instead of one ncclReduce
+ *   PHOTON_STEP_SCALE=<k>   integrator step = k x smallest grid spacing (the reference has k = 1 only)
+ *   PHOTON_FULL_DEPTH=1     keep more than the 1024 z-planes the reference keeps (trace.h:2037-2038)
  */
 #ifndef PHOTON_B200_H_
 #define PHOTON_B200_H_
@@ -168,6 +175,15 @@ int photon_b200_mie_irradiance_table(const double *particle_sizes, int num_sizes
  * the GPU and copies it back.  meta16 = {min xyz, max xyz, spacing xyz, step, data_min, W, H, D, 0, 0}.
  * out may be NULL to query the size. */
 int photon_b200_load_field(const char *path, float meta16[16], float *out_float4, long long capacity_voxels);
+
+/* A density volume handed over in memory instead of an NRRD file: rho[nz][ny][nx] float32 (x fastest) in host
+ * memory or on any device of the box, spacing / origin (x, y, z, um) as the NRRD header would give them
+ * (`spacings`, `space origin`: loadNRRD, trace.h:1663-1817).  Afterwards density_grad_filename "mem:<name>" selects it.
+ * The array must stay valid until every device that traces with it has built its field (first call per device);
+ * registering the name again invalidates the cached fields. */
+int photon_b200_register_field(const char *name, const float *rho, int nx, int ny, int nz,
+                               const double spacing[3], const double origin[3]);
+int photon_b200_unregister_field(const char *name);
 
 /* Cubic mode (PHOTON_INTERPOLATION=cubic): the B-spline coefficient volume of n-1 (float[D][H][W]),
  * prefiltered on the GPU (replaces CubicBSplinePrefilter3DTimer, trace.h:1655).  out may be NULL. */

@@ -77,12 +77,41 @@ struct DeviceField {
 std::mutex g_field_mutex;
 std::vector<DeviceField *> g_fields;     // one cache entry per device
 
+// Fields registered from memory (photon_b200_register_field): density_grad_filename "mem:<name>" resolves
+// here instead of the file system -- for synthetic fields that would otherwise make a round trip through a
+// multi-GiB NRRD file.  The caller keeps the array alive until every device that uses it has built its field.
+struct MemField { const float *rho; int nx, ny, nz; double spacing[3], origin[3]; long long version; };
+std::mutex g_mem_mutex;
+std::vector<std::pair<std::string, MemField>> g_mem_fields;
+long long g_mem_version = 0;
+bool find_mem_field(const char *path, MemField &out) {
+    if (strncmp(path, "mem:", 4) != 0) return false;
+    std::lock_guard<std::mutex> lk(g_mem_mutex);
+    for (auto &e : g_mem_fields) if (e.first == path + 4) { out = e.second; return true; }
+    return false;
+}
+
 bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) {
     pnrrd::Volume vol;
-    if (!pnrrd::load(path, vol)) {
-        g_error = std::string("failed to load \"") + path + "\": " + vol.error;
-        fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
-        return false;
+    MemField mem{};
+    const bool from_memory = strncmp(path, "mem:", 4) == 0;
+    const float *src = nullptr;
+    if (from_memory) {
+        if (!find_mem_field(path, mem)) {
+            g_error = std::string("no field registered as \"") + path + "\"";
+            fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
+            return false;
+        }
+        vol.nx = mem.nx; vol.ny = mem.ny; vol.nz = mem.nz;
+        for (int i = 0; i < 3; i++) { vol.spacing[i] = mem.spacing[i]; vol.origin[i] = mem.origin[i]; }
+        src = mem.rho;
+    } else {
+        if (!pnrrd::load(path, vol)) {
+            g_error = std::string("failed to load \"") + path + "\": " + vol.error;
+            fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
+            return false;
+        }
+        src = vol.rho.data();
     }
     int sx = vol.nx, sy = vol.ny, sz = vol.nz;
     // bounds from the header (trace.h:1698-1706); NRRD z origin is shifted by -750e3
@@ -106,16 +135,27 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
     step = step < dz ? step : (float)dz;
     P.step = step;
     size_t n = (size_t)sx * sy * sz;
-    if (n >= ((size_t)1 << 32)) {        // the sampler indexes voxels with 32 bits (ray_stages.cuh)
-        g_error = "density field has 2^32 voxels or more; not supported by this build";
+    if (n > ((size_t)1 << 32)) {         // the sampler indexes voxels with 32 bits (ray_stages.cuh): indices 0 .. 2^32-1
+        g_error = "density field has more than 2^32 voxels; not supported by this build";
         fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
         return false;
     }
     float *d_rho = nullptr; unsigned int *d_min = nullptr;
-    CK(cudaMalloc(&d_rho, n * sizeof(float)));
+    // a registered array that already lives on this device is read in place; anything else (host memory, another
+    // device: unified addressing) is copied next to the texels first
+    bool in_place = false;
+    if (from_memory) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device == device) in_place = true;
+        cudaGetLastError();
+    }
     CK(cudaMalloc(&F.lin, n * sizeof(f4)));
     CK(cudaMalloc(&d_min, sizeof(unsigned int)));
-    CK(cudaMemcpyAsync(d_rho, vol.rho.data(), n * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (in_place) d_rho = const_cast<float *>(src);
+    else {
+        CK(cudaMalloc(&d_rho, n * sizeof(float)));
+        CK(cudaMemcpyAsync(d_rho, src, n * sizeof(float), cudaMemcpyDefault, st));
+    }
     CK(cudaMemsetAsync(d_min, 0xff, sizeof(unsigned int), st));
     int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)148 * 16);
     build_field_kernel<<<blocks, 256, 0, st>>>(d_rho, F.lin, sx, sy, sz, (float)dx, (float)dy, (float)dz, d_min);
@@ -123,7 +163,8 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
     unsigned int key = 0;
     CK(cudaMemcpyAsync(&key, d_min, sizeof key, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    cudaFree(d_rho); cudaFree(d_min);
+    if (!in_place) cudaFree(d_rho);
+    cudaFree(d_min);
     P.data_min = float_from_order_key(key);
     P.skip_step = P.step / (1 + P.data_min);
     F.P = P; F.device = device; F.path = path; F.spacing = mk3((float)dx, (float)dy, (float)dz);
@@ -169,6 +210,7 @@ DeviceField *get_field(const char *path, int device, cudaStream_t st) {
     struct stat sb;
     long long mt = 0, fs = 0;
     if (stat(path, &sb) == 0) { mt = (long long)sb.st_mtim.tv_sec * 1000000000LL + sb.st_mtim.tv_nsec; fs = (long long)sb.st_size; }
+    { MemField m{}; if (find_mem_field(path, m)) { mt = m.version; fs = (long long)m.nx * m.ny * m.nz; } }
     DeviceField *slot = nullptr;
     {
         std::lock_guard<std::mutex> lk(g_field_mutex);
@@ -362,6 +404,23 @@ extern "C" {
 
 int photon_b200_abi_version(void) { return 1; }
 
+int photon_b200_register_field(const char *name, const float *rho, int nx, int ny, int nz,
+                               const double spacing[3], const double origin[3]) {
+    g_error.clear();
+    if (!name || !*name || !rho || nx < 3 || ny < 3 || nz < 3 || !spacing || !origin) { g_error = "register_field: bad arguments"; return 1; }
+    MemField m{rho, nx, ny, nz, {spacing[0], spacing[1], spacing[2]}, {origin[0], origin[1], origin[2]}, 0};
+    std::lock_guard<std::mutex> lk(g_mem_mutex);
+    m.version = ++g_mem_version;
+    for (auto &e : g_mem_fields) if (e.first == name) { e.second = m; return 0; }
+    g_mem_fields.emplace_back(std::string(name), m);
+    return 0;
+}
+int photon_b200_unregister_field(const char *name) {
+    std::lock_guard<std::mutex> lk(g_mem_mutex);
+    for (size_t i = 0; i < g_mem_fields.size(); i++) if (name && g_mem_fields[i].first == name) { g_mem_fields.erase(g_mem_fields.begin() + i); return 0; }
+    return 1;
+}
+
 // ---- source-point generation (host; replaces the Python loops of run_simulation_02.py) ----
 long long photon_b200_sunflower(double diameter, double count, const double *ring_phase_u, double *x, double *y, long long capacity) {
     g_error.clear();
@@ -502,6 +561,11 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         s->field = get_field(density_grad_filename, s->device, s->stream);
         if (!s->field) return false;
         a.field = s->field->P;
+        // extension (BASELINE C5's step-size sweep; the reference always steps by the smallest spacing, trace.h:2086-2098)
+        if (const char *e = getenv("PHOTON_STEP_SCALE")) {
+            const double k = atof(e);
+            if (k > 0.0) { a.field.step = (float)((double)a.field.step * k); a.field.skip_step = a.field.step / (1 + a.field.data_min); }
+        }
         // coherent rays: the cone of a source point at the lens (cone_ratio * lens_pitch) is narrower than a cell
         s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
         if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;

@@ -62,6 +62,10 @@ def load_library(require_gpu=False):
         lib.photon_b200_load_field.restype = C.c_int
         lib.photon_scene_trace_range.argtypes = [C.c_void_p, C.c_int, C.c_int]
         lib.photon_scene_trace_range.restype = C.c_int
+        lib.photon_b200_register_field.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        lib.photon_b200_register_field.restype = C.c_int
+        lib.photon_b200_unregister_field.argtypes = [C.c_char_p]
+        lib.photon_b200_unregister_field.restype = C.c_int
         lib.photon_scene_export_u16.argtypes = [C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_float, C.c_uint, C.c_void_p]
         lib.photon_scene_export_u16.restype = C.c_int
         lib.photon_scene_enable_dot_stats.argtypes = [C.c_void_p, C.c_longlong]

@@ -61,3 +61,22 @@ def read_nrrd(path):
     spacings = tuple(float(t) for t in fields["spacings"].split())
     origin = tuple(float(t) for t in fields["space origin"].strip("()").split(","))
     return rho, spacings, origin
+
+
+def register_field(lib, name, rho, spacings, origin):
+    """Hand a density volume to the library in memory (photon_b200_register_field); afterwards
+    ``density_grad_filename = "mem:<name>"`` selects it.  ``rho``: float32 [z][y][x] numpy array (kept
+    alive by the returned handle) or a ``(device_pointer, (nz, ny, nx))`` pair for an array already on a GPU."""
+    import ctypes as C
+    if isinstance(rho, tuple):
+        ptr, (nz, ny, nx) = rho
+        keep = None
+    else:
+        keep = np.ascontiguousarray(rho, np.float32)
+        nz, ny, nx = keep.shape
+        ptr = keep.ctypes.data
+    sp = (C.c_double * 3)(*[float(v) for v in spacings])
+    og = (C.c_double * 3)(*[float(v) for v in origin])
+    if lib.photon_b200_register_field(name.encode(), C.c_void_p(int(ptr)), int(nx), int(ny), int(nz), sp, og) != 0:
+        raise RuntimeError(lib.photon_b200_last_error().decode())
+    return keep

@@ -290,3 +290,71 @@ def c4_piv(nrrd_path, *, n=1024, particles=1000000, rays_per_particle=1000, nx=2
     call.density_grad_filename = str(nrrd_path)
     call.ray_tracing_algorithm = 2
     return call
+
+
+def three_element_system(call, *, focal_length=105e3, f_number=11.0, separation=8e3, lens_radius=1e5):
+    """Replace the single lens of ``call`` (set by :func:`camera_and_lens`) by three sequential elements on
+    the same axis: thick lens (f = 2 focal_length), aperture stop, thick lens (f = 2 focal_length), spaced
+    ``separation`` / 2 apart around the original lens centre -- together about the original focal length
+    (1/f = 1/f1 + 1/f2 - d/(f1 f2)).  System indices 3, 2, 1 in the order the rays meet them
+    (prt.cu:1274-1381: stage s takes the element whose index is max - s)."""
+    z_lens = float(call.element_center[0][2])
+    pitch, t, n = solve_lens(2.0 * focal_length, 2.0 * f_number, lens_radius, "general")
+    elems, centers, planes = [], [], []
+    for kind, dz in ((b"l", +separation / 2.0), (b"a", 0.0), (b"l", -separation / 2.0)):
+        el = element_data_struct()
+        el.axial_offset_distances[0] = el.axial_offset_distances[1] = 0.0
+        el.element_number = float(len(elems) + 1)
+        el.element_type = kind
+        el.elements_coplanar = 0.0
+        el.z_inter_element_distance = 0.0
+        g = el.element_geometry
+        g.front_surface_radius, g.front_surface_spherical = lens_radius, True
+        g.back_surface_radius, g.back_surface_spherical = -lens_radius, True
+        g.pitch = pitch if kind == b"l" else 0.95 * pitch
+        g.vertex_distance = t if kind == b"l" else 500.0
+        p = el.element_properties
+        p.abbe_number, p.absorbance_rate, p.refractive_index = float("nan"), 0.0, n
+        p.thin_lens_focal_length, p.transmission_ratio = 2.0 * focal_length, 1.0
+        elems.append(el)
+        centers.append([0.0, 0.0, z_lens + dz])
+        planes.append([0.0, 0.0, 1.0, -(z_lens + dz)])
+    call.elements = elems
+    call.element_center = np.array(centers)
+    call.element_plane_parameters = np.array(planes)
+    call.element_system_index = np.array([3, 2, 1], np.int32)
+    return call
+
+
+def c5_stress(field, *, n=2048, nz=1024, dots_per_side=100, points_per_dot=100, rays_per_point=1000,
+              nx=1024, ny=1024, write_field=True, source_point_number=10000, lib=None):
+    """BOS through a Gaussian blob on an n x n x nz grid (the reference keeps at most
+    1024 z-planes, trace.h:2037-2038; 2048 x 2048 x 1024 = 2^32 voxels = 64 GiB of texels), three sequential
+    optical elements (:func:`three_element_system`), diffraction splat, RK4.  ``field``: an NRRD path, or
+    ``"mem:<name>"`` to hand the volume over in memory (``lib`` required; the returned call keeps it alive).
+    The step-size sweep of C5 is ``PHOTON_STEP_SCALE`` = 1, 0.5, 0.25."""
+    from .nrrd import register_field, write_nrrd
+    call = RayTracingCall()
+    z_object = camera_and_lens(call, focal_length=105e3, f_number=11.0, object_distance=1e6, lens_model="general",
+                               nx=nx, ny=ny, pixel_pitch=10.0, diffraction_diameter=3.0, implement_diffraction=True)
+    three_element_system(call, focal_length=105e3, f_number=11.0)
+    extent = 511 * 176.0
+    sx, sz = extent / (n - 1), extent / (nz - 1)
+    if write_field:
+        cx = (np.arange(n, dtype=np.float64) - (n - 1) / 2.0) * sx
+        cz = (np.arange(nz, dtype=np.float64) - (nz - 1) / 2.0) * sz
+        gx, gz = np.exp(-cx ** 2 / (2.0 * 15e3 ** 2)).astype(np.float32), np.exp(-cz ** 2 / (2.0 * 15e3 ** 2)).astype(np.float32)
+        rho = np.float32(1.225) + np.float32(0.5) * (gz[:, None, None] * gx[None, :, None] * gx[None, None, :])
+        origin = (-extent / 2, -extent / 2, 750e3 - extent / 2)
+        if str(field).startswith("mem:"):
+            call._field_keepalive = register_field(lib, str(field)[4:], rho, (sx, sx, sz), origin)
+        else:
+            write_nrrd(field, rho, (sx, sx, sz), origin)
+    bos_dots(call, z_object, dots_per_side=dots_per_side, extent=40e3, points_per_dot=points_per_dot, dot_diameter=300.0)
+    call.lightray_number_per_particle = rays_per_point
+    call.source_point_number = source_point_number
+    call.simulate_density_gradients = True
+    call.density_grad_filename = str(field)
+    call.ray_tracing_algorithm = 2
+    call.ray_cone_pitch_ratio = 1e-4
+    return call

@@ -6,6 +6,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from photon_b200 import scenes
 from photon_b200.scene import ResidentScene
 
+KEEP = {}
+
+
 def make(name, d):
     if name.startswith("c4"):                    # c4 or c4_<n>: BASELINE C4 (turbulent n^3 field, Mie, thick lens, 4 MP)
         import torch
@@ -24,6 +27,27 @@ def make(name, d):
             o = np.argsort(spread(qx) | (spread(qy) << 1), kind="stable")
             c.x, c.y, c.z, c.radiance, c.diameter_index = c.x[o], c.y[o], c.z[o], c.radiance[o], c.diameter_index[o]
         return c
+    if name.startswith("c5"):                    # c5 or c5_<n>: BASELINE C5 field (n x n x min(n, 1024) blob made on the GPU,
+        import torch                             # handed over in memory), three optical elements; PHOTON_STEP_SCALE sweeps the step
+        from photon_b200.lib import load_library
+        from photon_b200.nrrd import register_field
+        n = int(name.split("_")[1]) if "_" in name else 2048
+        nz = min(n, 1024)
+        extent = 511 * 176.0
+        sx, sz = extent / (n - 1), extent / (nz - 1)
+        if "c5" not in KEEP:
+            dev = torch.device("cuda")
+            cx = (torch.arange(n, dtype=torch.float64, device=dev) - (n - 1) / 2.0) * sx
+            cz = (torch.arange(nz, dtype=torch.float64, device=dev) - (nz - 1) / 2.0) * sz
+            gx = torch.exp(-cx ** 2 / (2.0 * 15e3 ** 2)).float(); gz = torch.exp(-cz ** 2 / (2.0 * 15e3 ** 2)).float()
+            rho = gz[:, None, None] * gx[None, :, None]
+            rho = rho * gx[None, None, :]
+            rho.mul_(0.5).add_(1.225)
+            torch.cuda.synchronize()
+            register_field(load_library(require_gpu=True), "c5", (rho.data_ptr(), (nz, n, n)), (sx, sx, sz),
+                           (-extent / 2, -extent / 2, 750e3 - extent / 2))
+            KEEP["c5"] = rho
+        return scenes.c5_stress("mem:c5", n=n, nz=nz, write_field=False)
     if name.startswith("piv"):
         c = scenes.c1_piv(particles=20000, rays_per_particle=10000)
         if name == "piv_diffraction":
