@@ -35,7 +35,8 @@ def make(name, d):
         nz = min(n, 1024)
         extent = 511 * 176.0
         sx, sz = extent / (n - 1), extent / (nz - 1)
-        if "c5" not in KEEP:
+        tag = "c5_%d" % n
+        if tag not in KEEP:
             dev = torch.device("cuda")
             cx = (torch.arange(n, dtype=torch.float64, device=dev) - (n - 1) / 2.0) * sx
             cz = (torch.arange(nz, dtype=torch.float64, device=dev) - (nz - 1) / 2.0) * sz
@@ -44,10 +45,11 @@ def make(name, d):
             rho = rho * gx[None, None, :]
             rho.mul_(0.5).add_(1.225)
             torch.cuda.synchronize()
-            register_field(load_library(require_gpu=True), "c5", (rho.data_ptr(), (nz, n, n)), (sx, sx, sz),
+            register_field(load_library(require_gpu=True), tag, (rho.data_ptr(), (nz, n, n)), (sx, sx, sz),
                            (-extent / 2, -extent / 2, 750e3 - extent / 2))
-            KEEP["c5"] = rho
-        return scenes.c5_stress("mem:c5", n=n, nz=nz, write_field=False)
+            KEEP.clear()                          # one big volume at a time
+            KEEP[tag] = rho
+        return scenes.c5_stress("mem:" + tag, n=n, nz=nz, write_field=False)
     if name.startswith("piv"):
         c = scenes.c1_piv(particles=20000, rays_per_particle=10000)
         if name == "piv_diffraction":
@@ -67,7 +69,11 @@ def make(name, d):
 
 d = "/tmp/photon_bench"; os.makedirs(d, exist_ok=True)
 for name in (sys.argv[1:] or ["piv", "piv_thin", "piv_diffuse", "piv_diffraction", "bos_nograd", "bos_euler"]):
-    call = make(name, d)
+    if "@" in name:                              # <workload>@<k>: integrator step = k x smallest spacing
+        os.environ["PHOTON_STEP_SCALE"] = name.split("@")[1]
+    else:
+        os.environ.pop("PHOTON_STEP_SCALE", None)
+    call = make(name.split("@")[0], d)
     s = ResidentScene(call)
     n = min(s.num_points, 10000)
     for k in range(2):
