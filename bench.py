@@ -354,7 +354,11 @@ def main():
                                         "MEASURED_PEAKS.json has no FP32 figure",
                          "l1_bytes_per_ray_step": L1_BYTES_PER_RAY_STEP,
                          "l1_gbs_achieved": steps_per_launch * L1_BYTES_PER_RAY_STEP / (k_ms * 1e-3) / 1e9,
-                         "hbm_peak_gbs_measured": peaks.get("hbm_gbs")},
+                         "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
+                         # what ncu --set full reported for this kernel and command (not measured in this run)
+                         "ncu": {"issue_slots_busy": 0.664, "fma_pipe_busy": 0.605, "dram_throughput": 0.002,
+                                 "l1_hit_rate": 0.958, "warp_instructions_per_ray_step": 239,
+                                 "source": "profiles/r2b_trace_details.txt"} if not CUBIC else None},
         }
         if not args.no_cpu_baseline and world == 1:
             cl, kind = cpu_reference_lib()
