@@ -65,10 +65,9 @@ struct SensorSample {
     int sflags;                          // bit 0: sdir set, bit 1: spos set
 };
 
-template <bool DUMP, class Sampler, bool STATS = false>
-PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr,
-                                                  long long gid, bool save, unsigned long long &steps) {
-    SensorSample out; out.valid = false; out.d_x = out.d_y = 0; out.radiance = 0; out.c4 = 0; out.sflags = 0;
+// The per-ray pipeline in three pieces: generation (+ the move into the volume frame), the march, everything
+// after it (back to the camera frame, lens system, sensor).
+PH_HD Ray ray_prologue(const TraceArgs &a, int p, int lr, NormalStream &ns) {
     float x_lens, y_lens;
     unsigned long long ray_index = (unsigned long long)(p + a.global_point_offset) * (unsigned long long)a.rpp + (unsigned long long)lr;
     if (a.rpp == 1) { x_lens = 0.0f; y_lens = 0.0f; }
@@ -77,21 +76,23 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
         philox4x32_10(c, a.seed, 0x50484f54u);
         lens_aim(a.cone_ratio, a.lens_pitch, u01_24(c[0]), u01_24(c[1]), x_lens, y_lens);
     } else { x_lens = PH_LDG(&a.aim[lr].x); y_lens = PH_LDG(&a.aim[lr].y); }
-    NormalStream ns; ns.ray = ray_index; ns.ctr = 0; ns.seed = a.seed;
-
+    ns.ray = ray_index; ns.ctr = 0; ns.seed = a.seed;
     Ray ray = generate_ray(a.image_distance, a.mie, PH_LDG(&a.sx[p]), PH_LDG(&a.sy[p]), PH_LDG(&a.sz[p]),
                            PH_LDG(&a.sradiance[p]), PH_LDG(&a.sdiam[p]), a.wavelength, a.inv_fnum2, x_lens, y_lens);
-    if (a.simulate_gradients) {                                          // prt.cu:2033-2131
+    if (a.simulate_gradients) {                                          // prt.cu:2033-2076
         f3 rp = ray.pos;
         rp.z = (float)((double)rp.z - a.z_shift);
         ray.pos = mat_mul(a.cam.inv_rot, rp);
         ray.dir = mat_mul(a.cam.inv_rot, ray.dir);
-        IntermediateDump im; im.n = 0; im.pos = nullptr; im.dir = nullptr;
-        if (DUMP && a.inter_pos && gid < a.n_save) {
-            im.pos = a.inter_pos + (size_t)gid * a.n_inter; im.dir = a.inter_dir + (size_t)gid * a.n_inter; im.n = a.n_inter;
-        }
-        steps += (unsigned long long)trace_volume<DUMP>(ray, a.field, S, a.algorithm, im, a.add_ngrad_noise != 0, a.ngrad_noise_std, ns);
-        rp = mat_mul(a.cam.rot, ray.pos);
+    }
+    return ray;
+}
+
+template <bool DUMP, bool STATS>
+PH_HD SensorSample ray_epilogue(const TraceArgs &a, Ray &ray, NormalStream &ns, long long gid, bool save) {
+    SensorSample out; out.valid = false; out.d_x = out.d_y = 0; out.radiance = 0; out.c4 = 0; out.sflags = 0;
+    if (a.simulate_gradients) {                                          // prt.cu:2100-2131
+        f3 rp = mat_mul(a.cam.rot, ray.pos);
         ray.dir = normalize(mat_mul(a.cam.rot, ray.dir));
         rp.z = (float)((double)rp.z + a.z_shift);
         ray.pos = rp;
@@ -130,6 +131,20 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
     return out;
 }
 
+template <bool DUMP, class Sampler, bool STATS = false>
+PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr,
+                                                  long long gid, bool save, unsigned long long &steps) {
+    NormalStream ns;
+    Ray ray = ray_prologue(a, p, lr, ns);
+    if (a.simulate_gradients) {
+        IntermediateDump im; im.n = 0; im.pos = nullptr; im.dir = nullptr;
+        if (DUMP && a.inter_pos && gid < a.n_save) {
+            im.pos = a.inter_pos + (size_t)gid * a.n_inter; im.dir = a.inter_dir + (size_t)gid * a.n_inter; im.n = a.n_inter;
+        }
+        steps += (unsigned long long)trace_volume<DUMP>(ray, a.field, S, a.algorithm, im, a.add_ngrad_noise != 0, a.ngrad_noise_std, ns);
+    }
+    return ray_epilogue<DUMP, STATS>(a, ray, ns, gid, save);
+}
 
 // One voxel of the (grad n, n-1) field: Gladstone-Dale n-1 = K rho (trace.h:1729-1748) and
 // finite-difference gradients, one-sided 2nd order at the faces and central inside
