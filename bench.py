@@ -356,9 +356,9 @@ def main():
                          "l1_gbs_achieved": steps_per_launch * L1_BYTES_PER_RAY_STEP / (k_ms * 1e-3) / 1e9,
                          "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
                          # what ncu --set full reported for this kernel and command (not measured in this run)
-                         "ncu": {"issue_slots_busy": 0.664, "fma_pipe_busy": 0.605, "dram_throughput": 0.002,
-                                 "l1_hit_rate": 0.958, "warp_instructions_per_ray_step": 239,
-                                 "source": "profiles/r2b_trace_details.txt"} if not CUBIC else None},
+                         "ncu": {"issue_slots_busy": 0.666, "fma_pipe_busy": 0.601, "dram_throughput": 0.002,
+                                 "l1_hit_rate": 0.957, "warp_instructions_per_ray_step": 239,
+                                 "source": "profiles/r2p_trace_details.txt"} if not CUBIC else None},
         }
         if not args.no_cpu_baseline and world == 1:
             cl, kind = cpu_reference_lib()
