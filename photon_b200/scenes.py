@@ -255,7 +255,7 @@ def turbulent_field(n, *, seed=1, k_lo=4.0, k_hi=128.0, rms=0.05, rho0=1.225, de
     F = np.fft.rfftn(w)
     k = np.sqrt(kz[:, None, None] ** 2 + kz[None, :, None] ** 2 + kx[None, None, :] ** 2)
     amp = np.where((k >= k_lo) & (k <= k_hi), np.maximum(k, 1.0) ** (-11.0 / 6.0), 0.0)
-    f = np.fft.irfftn(F * amp, s=(n, n, n))
+    f = np.fft.irfftn(F * amp, s=(n, n, n), axes=(0, 1, 2))
     f *= rms / f.std()
     return (f + rho0).astype(np.float32)
 
