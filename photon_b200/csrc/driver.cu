@@ -130,7 +130,6 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
         { double k[3] = {(double)P.scale.x * (sx - 2), (double)P.scale.y * (sy - 2), (double)P.scale.z * (sz - 2)};
           P.tk = mk3((float)k[0], (float)k[1], (float)k[2]);
           P.tc = mk3((float)(0.5 - (double)P.mn.x * k[0]), (float)(0.5 - (double)P.mn.y * k[1]), (float)(0.5 - (double)P.mn.z * k[2])); } P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
-    P.cell_hi = mk3(12582912.0f + (float)(sx - 3), 12582912.0f + (float)(sy - 3), 12582912.0f + (float)(sz - 3));
     float step = (float)fmin(dx, dy);
     step = step < dz ? step : (float)dz;
     P.step = step;

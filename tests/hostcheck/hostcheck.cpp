@@ -66,7 +66,6 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
         { double k[3] = {(double)P.scale.x * (sx - 2), (double)P.scale.y * (sy - 2), (double)P.scale.z * (sz - 2)};
           P.tk = mk3((float)k[0], (float)k[1], (float)k[2]);
           P.tc = mk3((float)(0.5 - (double)P.mn.x * k[0]), (float)(0.5 - (double)P.mn.y * k[1]), (float)(0.5 - (double)P.mn.z * k[2])); } P.wm2 = (float)(sx - 2); P.hm2 = (float)(sy - 2); P.dm2 = (float)(sz - 2);
-    P.cell_hi = mk3(12582912.0f + (float)(sx - 3), 12582912.0f + (float)(sy - 3), 12582912.0f + (float)(sz - 3));
         float step = (float)fmin(dx, dy); step = step < dz ? step : (float)dz; P.step = step;
         field.resize((size_t)sx * sy * sz);
         float dmin = INFINITY;

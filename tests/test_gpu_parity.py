@@ -69,3 +69,37 @@ def test_texture_sampler_close_to_linear(cases, cuda_lib, monkeypatch, tmp_path)
     m = util.compare(lin, tex, pitch)
     print("texture vs linear", m)
     assert m["dpos_px"] <= 5e-3 and m["ddir_rad"] <= 1e-5, m
+
+
+def _intermediate(d, kind):
+    import glob, os
+    return np.concatenate([np.fromfile(f, np.float32).reshape(-1, 3)
+                           for f in sorted(glob.glob(os.path.join(d, "intermediate_%s_*.bin" % kind)))])
+
+
+@pytest.mark.parametrize("name", ["bos_rk4_thin_diffraction", "bos_euler_thin_diffraction"])
+def test_generic_marcher_and_intermediate_dumps(name, cases, cuda_lib, oracle_lib, tmp_path):
+    """With final-ray dumps only, the marchers run their hot loops (rk4_hot_loop / euler_hot_loop -- the code the
+    benchmark times), which is what every other test in this file compares with the oracle.  Intermediate dumps
+    (prt.cu:3613-3670) force every step through the generic path: the same scenes that way, the first positions
+    and directions along each ray included, and the two marchers against each other."""
+    call, pitch = cases[name]
+    for k in "ogh":
+        (tmp_path / k).mkdir()
+    hot = util.run_with_dumps(cuda_lib, call, str(tmp_path / "h"))
+    call.save_intermediate_ray_data = True
+    call.num_intermediate_positions_save = 6
+    try:
+        ref = util.run_with_dumps(oracle_lib, call, str(tmp_path / "o"))
+        got = util.run_with_dumps(cuda_lib, call, str(tmp_path / "g"))
+    finally:
+        call.save_intermediate_ray_data = False
+        call.num_intermediate_positions_save = 0
+    util.assert_parity(name + " generic", util.compare(ref, got, pitch))
+    util.assert_parity(name + " hot vs generic", util.compare(got, hot, pitch))
+    for kind, tol in (("pos", 0.25), ("dir", 1e-6)):                     # um (positions are ~1e5..1e6 um: 4 ulp), -
+        a, b = _intermediate(str(tmp_path / "o"), kind), _intermediate(str(tmp_path / "g"), kind)
+        assert a.shape == b.shape and len(a) == 6 * len(ref[1])
+        assert np.array_equal(np.isnan(a), np.isnan(b))
+        ok = np.isfinite(a)
+        assert ok.mean() > 0.5 and np.abs(a[ok] - b[ok]).max() <= tol, (kind, np.abs(a[ok] - b[ok]).max())
