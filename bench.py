@@ -36,11 +36,12 @@ CUBIC = os.environ.get("PHOTON_INTERPOLATION", "linear") == "cubic"
 FLOP_PER_RAY_STEP = 1434.0 if CUBIC else 330.0
 L1_BYTES_PER_RAY_STEP = 768.0 if CUBIC else 384.0    # linear: 3 samples x 8 texels x 16 B
 # dram__bytes_read.sum + dram__bytes_write.sum of one trace launch from the ncu --set full capture under
-# profiles/ (r3b_trace_raw_selected.txt: 16.7 MB read + 856.0 MB written, linear mode, default variant);
+# profiles/ (r3h_trace_raw_selected.txt: 16.8 MB read + 849.6 MB written, linear mode, default variant);
 # None where no capture of this mode exists.  The writes are L2 evictions of the kernel's local-memory
-# window (three spilled registers of the hot loop at the 80-register cap), 17 GB/s = 0.3 % of HBM; the
+# window (1168 B of stack per thread for the out-of-line generic step and the splat footprints, 133 MB
+# resident, competing for the 126 MB L2 with the field streaming through it): 17 GB/s = 0.3 % of HBM.  The
 # algorithmic HBM bytes per launch are ~4.4 MB (source points + one flush of the 4 MiB image).
-NCU_DRAM_BYTES_PER_LAUNCH = None if CUBIC else 872682752
+NCU_DRAM_BYTES_PER_LAUNCH = None if CUBIC else 866407936
 
 
 def parse():
@@ -359,9 +360,9 @@ def main():
                          "l1_gbs_achieved": steps_per_launch * L1_BYTES_PER_RAY_STEP / (k_ms * 1e-3) / 1e9,
                          "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
                          # what ncu --set full reported for this kernel and command (not measured in this run)
-                         "ncu": {"issue_slots_busy": 0.672, "fma_pipe_busy": 0.612, "dram_throughput": 0.002,
-                                 "l1_hit_rate": 0.944, "warp_instructions_per_ray_step": 239,
-                                 "source": "profiles/r3b_trace_details.txt, r3b_trace_raw_selected.txt"} if not CUBIC else None},
+                         "ncu": {"issue_slots_busy": 0.672, "fma_pipe_busy": 0.622, "dram_throughput": 0.002,
+                                 "l1_hit_rate": 0.894, "warp_instructions_per_ray_step": 241,
+                                 "source": "profiles/r3h_trace_details.txt, r3h_trace_raw_selected.txt"} if not CUBIC else None},
         }
         if not args.no_cpu_baseline and world == 1:
             cl, kind = cpu_reference_lib()
