@@ -13,11 +13,11 @@ Host-side mirror of the callers above the hot path, with the reference's functio
   * ``prepare_call``                              perform_ray_tracing_03.py:1949-2187 and :1631-1947 --
     everything perform_ray_tracing_03 computes before the ctypes call, as a RayTracingCall
   * ``perform_ray_tracing_03``                    perform_ray_tracing_03.py:1949-2259 (call + image export)
-  * ``run_simulation_02``                         run_simulation_02.py:1725-2110, 'piv' and 'bos' branches
+  * ``run_simulation_02``                         run_simulation_02.py:1725-2110, 'piv', 'cal' and 'bos' branches
 
 Source points come from :mod:`photon_b200.source_points`, the Mie table from :mod:`photon_b200.mie`,
-the trace and the 16-bit export run in the CUDA library (no numpy fallback for either).  The
-calibration branch ('cal') needs a target image the reference does not ship and is not mirrored.
+the trace and the 16-bit export run in the CUDA library (no numpy fallback for either).  ``generate_bos_image_lightfield_data``
+(a BOS target read from an image; never called by the reference's run loop either) lives in source_points too.
 Random draws: the reference uses numpy's global generator; pass ``rng`` (a ``RandomState``) to pin them.
 """
 import os
@@ -281,7 +281,7 @@ def _dump_dirs(simulation_parameters, image_directory, name):
 
 
 def run_simulation_02(simulation_parameters, rng=None, write_images=True):
-    """The 'piv' and 'bos' branches of rs02.py:1725-2110.  Returns a list of (name, I, I_raw); raw images
+    """The 'piv', 'cal' and 'bos' branches of rs02.py:1725-2110.  Returns a list of (name, I, I_raw); raw images
     are also written as ``<image_directory>/raw/<name>.bin`` like the reference (TIFF writing is left to the
     caller: the 16-bit arrays are what the reference hands to ``TIFF.imsave``)."""
     sp = simulation_parameters
@@ -329,6 +329,18 @@ def run_simulation_02(simulation_parameters, rng=None, write_images=True):
             I, I_raw = perform_ray_tracing_03(sp, optical_system, pixel_gain, float("nan"), "diffuse", src, "calibration")
             emit("bos_pattern_image_%d" % number, I, I_raw)
         sp["bos_pattern"]["x_grid_point_coordinate_vector"], sp["bos_pattern"]["y_grid_point_coordinate_vector"] = gx, gy
+    elif sp["simulation_type"] == "cal":                                               # rs02.py:1877-1953
+        cg = sp["calibration_grid"]
+        if not cg["generate_calibration_grid_images"]:
+            return results
+        for plane_index in range(1, int(cg["calibration_plane_number"]) + 1):
+            src = _sp.generate_calibration_lightfield_data(sp, optical_system, plane_index - 1, rng)
+            src["lightray_number_per_particle"] = cg["lightray_number_per_particle"]
+            src["lightray_process_number"] = cg["lightray_process_number"]
+            if sp["output_data"].get("save_lightrays", True):
+                _dump_dirs(sp, image_directory, "plane%02d" % plane_index)
+            I, I_raw = perform_ray_tracing_03(sp, optical_system, pixel_gain, float("nan"), "diffuse", src, "calibration")
+            emit("calibration_image_plane_%04d" % plane_index, I, I_raw)
     else:
-        raise ValueError("simulation_type %r: only 'piv' and 'bos' are built" % (sp["simulation_type"],))
+        raise ValueError("simulation_type %r: 'piv', 'bos' and 'cal' are built" % (sp["simulation_type"],))
     return results

@@ -182,3 +182,64 @@ def generate_piv_lightfield_data(simulation_parameters, optical_system, rotation
     return {"x": x, "y": y, "z": z, "radiance": rad, "diameter_index": diam, "source_point_number": 10000,
             "lightray_number_per_particle": pf["lightray_number_per_particle"], "num_particles": n,
             "z_offset": z_object - ld["object_distance"], "object_distance": ld["object_distance"]}
+
+
+def rotate_coordinates(X, Y, Z, Alpha, Beta, Gamma, XC, YC, ZC):
+    """rs02.py:395-444: rotation about (XC, YC, ZC) by R = Rx * Ry * Rz."""
+    from .scenes import rotation_matrix
+    W = np.dot(rotation_matrix(Alpha, Beta, Gamma), np.array([X - XC, Y - YC, Z - ZC]))
+    return [W[0] + XC, W[1] + YC, W[2] + ZC]
+
+
+def generate_calibration_lightfield_data(simulation_parameters, optical_system, plane_index, rng=None):
+    """rs02.py:1057-1249: one plane of the calibration target -- a regular grid of dots filled with sunflower
+    points (x index outer, y index inner), two quarter-size origin markers at (-dx/2, 0) and (0, +dy/2), the plane
+    at ``calibration_plane_spacing * (plane_index - (planes - 1) / 2)`` from the object plane, rotated by the
+    camera angles about the world origin."""
+    cg, cam, ld = simulation_parameters["calibration_grid"], simulation_parameters["camera_design"], simulation_parameters["lens_design"]
+    planes = int(cg["calibration_plane_number"])
+    nxg, nyg = int(cg["x_grid_point_number"]), int(cg["y_grid_point_number"])
+    per_dot = int(cg["particle_number_per_grid_point"])
+    z_object = object_plane(simulation_parameters, optical_system)
+    plane_z = cg["calibration_plane_spacing"] * np.linspace(-(planes - 1.0) / 2.0, (planes - 1.0) / 2.0, planes, endpoint=True)
+    vx = cg["x_grid_point_spacing"] * np.linspace(-(nxg - 1.0) / 2.0, (nxg - 1.0) / 2.0, nxg, endpoint=True)
+    vy = cg["y_grid_point_spacing"] * np.linspace(-(nyg - 1.0) / 2.0, (nyg - 1.0) / 2.0, nyg, endpoint=True)
+    r = _rng(rng)
+    ox, oy = calculate_sunflower_coordinates(cg["grid_point_diameter"], per_dot, r)
+    gx, gy = np.repeat(vx, nyg), np.tile(vy, nxg)
+    x = (gx[:, None] + ox[None, :]).reshape(-1)
+    y = (gy[:, None] + oy[None, :]).reshape(-1)
+    mx, my = calculate_sunflower_coordinates(cg["grid_point_diameter"] / 4, per_dot / 16, r)
+    x = np.concatenate([x, mx - cg["x_grid_point_spacing"] / 2.0, mx + 0])
+    y = np.concatenate([y, my + 0, my + cg["y_grid_point_spacing"] / 2.0])
+    z = plane_z[plane_index] * np.ones(x.shape)
+    x, y, z = rotate_coordinates(x, y, z, cam["x_camera_angle"], cam["y_camera_angle"], 0.0, 0.0, 0.0, 0.0)
+    return {"x": x, "y": y, "z": z + z_object, "radiance": np.ones(x.shape), "diameter_index": np.ones(x.shape),
+            "source_point_number": 10000, "z_offset": z_object - ld["object_distance"], "object_distance": ld["object_distance"]}
+
+
+def generate_bos_image_lightfield_data(simulation_parameters, optical_system, image=None):
+    """rs02.py:1554-1697: a BOS target given as an image -- every pixel > 0 of channel 0 becomes one source point
+    at its pixel centre (x mirrored), its grey value the radiance, the image spanning +-75 mm; then the camera
+    rotation.  ``image`` is the array ``mpimg.imread`` would return ([rows][cols][channels] or [rows][cols]) or a
+    file name (the reference reads a fixed ``./bos_pattern_black_dot_936.png`` that it does not ship).  The
+    reference's dict lacks ``z_offset`` / ``object_distance``, which the ctypes layer needs; they are added."""
+    cam, ld = simulation_parameters["camera_design"], simulation_parameters["lens_design"]
+    if image is None or isinstance(image, str):
+        import matplotlib.image as mpimg
+        image = mpimg.imread(image or "./bos_pattern_black_dot_936.png")
+    img = np.asarray(image)
+    if img.ndim == 3:
+        img = img[:, :, 0]
+    z_object = object_plane(simulation_parameters, optical_system)
+    X_Min, X_Max, Y_Max = -7.5e4, +7.5e4, +7.5e4
+    height, width = img.shape
+    pixel_width = (X_Max - X_Min) / width
+    rc = np.argwhere(img > 0)
+    x = X_Min + (width - rc[:, 1]) * pixel_width + pixel_width / 2.0
+    y = Y_Max - (rc[:, 0] * pixel_width + pixel_width / 2.0)
+    radiance = img[img > 0].astype(np.float64)
+    x, y, z = rotate_coordinates(x, y, 0.0 * np.ones(x.shape), cam["x_camera_angle"], cam["y_camera_angle"], 0.0, 0.0, 0.0, 0.0)
+    return {"x": x, "y": y, "z": z + z_object, "radiance": radiance, "diameter_index": np.ones(x.shape),
+            "source_point_number": min(10000, x.size), "z_offset": z_object - ld["object_distance"],
+            "object_distance": ld["object_distance"]}

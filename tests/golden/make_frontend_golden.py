@@ -1,7 +1,8 @@
 """Generates tests/golden/frontend_golden.npz from the reference's own function bodies in
 python_codes/run_simulation_02.py (taken unmodified with ast; numpy's global generator replaced by a seeded
 RandomState): the single-lens optical system solved from the two sample parameter files, and the log-normal
-particle diameter distribution / index draw of the PIV sample.
+particle diameter distribution / index draw of the PIV sample, and two planes of the calibration target
+(generate_calibration_lightfield_data) for the grid in ``calibration_parameters()``.
 Run in the build container only:  python tests/golden/make_frontend_golden.py"""
 import ast
 import os
@@ -17,7 +18,8 @@ from photon_b200.run_simulation import loadmat  # noqa: E402
 PATH = "/root/reference/python_codes/run_simulation_02.py"
 NAMES = {"create_single_lens_optical_system", "create_camera_optical_system", "log_normal_pdf", "inverse_log_normal_pdf",
          "log_normal_cdf", "calculate_log_normal_pdf_extrema", "calculate_particle_diameter_distribution",
-         "calculate_particle_diameter_indices"}
+         "calculate_particle_diameter_indices", "calculate_sunflower_coordinates", "rotate_coordinates",
+         "calculate_rotation_matrix", "generate_calibration_lightfield_data", "generate_bos_image_lightfield_data"}
 SEED = 77
 
 
@@ -59,6 +61,29 @@ d, pdf = ns["calculate_particle_diameter_distribution"](P)
 out["diameter_vector"], out["diameter_pdf"] = d, pdf
 P["particle_field"]["particle_number"] = 5000
 out["diameter_indices"] = ns["calculate_particle_diameter_indices"](P, pdf, d)
+from tests.test_run_simulation import calibration_parameters  # noqa: E402
+for plane in (0, 2):
+    ns["np"].random = PinnedRandom(SEED + plane)
+    C = calibration_parameters()
+    src = ns["generate_calibration_lightfield_data"](C, ns["create_camera_optical_system"](C), plane)
+    for k in ("x", "y", "z", "radiance", "diameter_index"):
+        out["cal%d_%s" % (plane, k)] = np.asarray(src[k], np.float64).reshape(-1)      # np.matrix rows -> flat
+    out["cal%d_z_offset" % plane] = src["z_offset"]
+from tests.test_run_simulation import target_image  # noqa: E402
+
+
+class ImreadStub:                                   # the reference reads a PNG it does not ship
+    @staticmethod
+    def imread(filename):
+        return target_image()
+
+
+ns["mpimg"] = ImreadStub
+C = calibration_parameters()
+src = ns["generate_bos_image_lightfield_data"](C, ns["create_camera_optical_system"](C))
+for k in ("x", "y", "z", "radiance", "diameter_index"):
+    out["img_%s" % k] = np.asarray(src[k], np.float64).reshape(-1)
+out["img_source_point_number"] = src["source_point_number"]
 out["seed"] = SEED
 np.savez_compressed(os.path.join(HERE, "frontend_golden.npz"), **out)
 print({k: np.asarray(v).shape for k, v in out.items()})

@@ -26,6 +26,28 @@ def parameters(kind):
     return rs.loadmat(os.path.join(G, "sample-parameters-%s.mat" % kind))
 
 
+def calibration_parameters():
+    """The PIV sample's lens and camera (tilted by a degree or two) with a 9 x 7 calibration grid on 3 planes."""
+    P = parameters("piv")
+    P["simulation_type"] = "cal"
+    P["camera_design"]["x_camera_angle"], P["camera_design"]["y_camera_angle"] = 0.02, -0.035
+    P["calibration_grid"] = {"generate_calibration_grid_images": 1, "calibration_plane_number": 3, "calibration_plane_spacing": 2.5e3,
+                             "grid_point_diameter": 1500.0, "x_grid_point_spacing": 8e3, "y_grid_point_spacing": 9e3,
+                             "x_grid_point_number": 9, "y_grid_point_number": 7, "particle_number_per_grid_point": 160,
+                             "lightray_number_per_particle": 50, "lightray_process_number": 1e6}
+    return P
+
+
+def target_image():
+    """A 60 x 48 RGBA float image with a few grey dots, as mpimg.imread returns a PNG."""
+    rng = np.random.RandomState(11)
+    img = np.zeros((48, 60, 4), np.float32)
+    for r, c in rng.randint(3, 45, size=(25, 2)):
+        img[r - 1:r + 2, c - 1:c + 2, :3] = rng.rand()
+    img[:, :, 3] = 1.0
+    return img
+
+
 def recorded_source(kind, P, optical_system, rec):
     block = P["bos_pattern" if kind == "bos" else "particle_field"]
     return {"x": rec.x, "y": rec.y, "z": rec.z, "radiance": rec.radiance, "diameter_index": rec.diameter_index,
@@ -92,11 +114,54 @@ def test_lens_solution_and_diameter_distribution_match_reference_functions():
     assert idx.max() <= 25                                   # the last bin is never assigned (rs02.py:624)
 
 
+@pytest.mark.parametrize("plane", [0, 2])
+def test_calibration_planes_match_reference_function(plane):
+    """generate_calibration_lightfield_data against the reference's own function body (rs02.py:1057-1249)."""
+    g = np.load(os.path.join(G, "frontend_golden.npz"))
+    P = calibration_parameters()
+    src = sp.generate_calibration_lightfield_data(P, rs.create_camera_optical_system(P), plane,
+                                                  np.random.RandomState(int(g["seed"]) + plane))
+    for k in ("x", "y", "z", "radiance", "diameter_index"):
+        want = g["cal%d_%s" % (plane, k)]
+        assert src[k].shape == want.shape, (k, src[k].shape, want.shape)
+        assert np.allclose(src[k], want, rtol=0, atol=1e-6 if k in "xyz" else 0), (k, np.abs(src[k] - want).max())
+    assert src["z_offset"] == float(g["cal%d_z_offset" % plane])
+    assert src["x"].size > 9 * 7 * 160                         # the grid plus the two origin markers
+
+
+def test_image_target_matches_reference_function():
+    """generate_bos_image_lightfield_data against the reference's function body with imread stubbed (rs02.py:1554-1697)."""
+    g = np.load(os.path.join(G, "frontend_golden.npz"))
+    P = calibration_parameters()
+    src = sp.generate_bos_image_lightfield_data(P, rs.create_camera_optical_system(P), target_image())
+    for k in ("x", "y", "z", "radiance", "diameter_index"):
+        want = g["img_%s" % k]
+        assert src[k].shape == want.shape and np.allclose(src[k], want, rtol=0, atol=1e-6 if k in "xyz" else 0), k
+    assert src["source_point_number"] == int(g["img_source_point_number"]) == src["x"].size < 10000
+
+
 def test_unknown_simulation_type_is_refused():
     P = parameters("bos")
-    P["simulation_type"] = "cal"
+    P["simulation_type"] = "holography"
     with pytest.raises(ValueError):
         rs.run_simulation_02(P, write_images=False)
+
+
+@pytest.mark.gpu
+def test_calibration_run_end_to_end(cuda_lib, tmp_path):
+    """'cal' branch: three planes, each image shows the dot grid (about 9 x 7 + 2 bright blobs) and the planes differ."""
+    P = calibration_parameters()
+    P["output_data"]["image_directory"] = str(tmp_path)
+    P["output_data"]["save_lightrays"] = 0
+    results = rs.run_simulation_02(P, rng=np.random.RandomState(5))
+    assert [r[0] for r in results] == ["calibration_image_plane_%04d" % i for i in (1, 2, 3)]
+    sums = []
+    for name, I, I_raw in results:
+        assert I.dtype == np.uint16 and I.max() == 65535 and I_raw.sum() > 0
+        lit = (I_raw > 0.05 * I_raw.max())
+        assert 0.001 < lit.mean() < 0.2, lit.mean()              # dots, not a flood
+        sums.append(float(I_raw.astype(np.float64).sum()))
+    assert not np.array_equal(results[0][2], results[2][2])
 
 
 @pytest.mark.gpu
