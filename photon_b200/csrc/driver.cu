@@ -63,6 +63,8 @@ struct DeviceField {
     f3 spacing{};
     f4 *lin = nullptr;                   // [D][H][W] float4 (grad n, n-1)
     float *coef = nullptr;               // cubic mode: [D][H][W] B-spline coefficients of n-1 (built on demand)
+    float4 *cells = nullptr;             // coherent hot loop: [D][H][W][8] per-cell polynomial table (built on demand)
+    bool cells_refused = false;          // it did not fit; do not try again for this field
     cudaArray_t arr = nullptr;           // optional 3-D array for the texture path
     cudaTextureObject_t tex = 0;
     void release() {
@@ -71,7 +73,8 @@ struct DeviceField {
         if (arr) cudaFreeArray(arr);
         if (lin) cudaFree(lin);
         if (coef) cudaFree(coef);
-        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; device = -1; path.clear();
+        if (cells) cudaFree(cells);
+        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; cells = nullptr; cells_refused = false; device = -1; path.clear();
     }
 };
 std::mutex g_field_mutex;
@@ -205,6 +208,29 @@ bool ensure_coefficients(DeviceField &F, cudaStream_t st) {
     return true;
 }
 
+// The per-cell polynomial table costs 128 B per voxel (8x the texels: 16 GiB at 512^3).  It is built when it fits
+// in PHOTON_CELLS_MAX_GIB (default 40) and leaves a quarter of the free memory alone; otherwise the coherent loop
+// reads the texels (LinearFieldCoherent).  Returns true when F.cells is there.
+bool ensure_cells(DeviceField &F, cudaStream_t st) {
+    if (F.cells) return true;
+    if (F.cells_refused) return false;
+    const size_t n = (size_t)F.P.W * F.P.H * F.P.D, bytes = n * 128;
+    double cap_gib = 40.0;
+    if (const char *e = getenv("PHOTON_CELLS_MAX_GIB")) cap_gib = atof(e);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || (double)bytes > cap_gib * 1073741824.0 || bytes > free_b - free_b / 4) {
+        cudaGetLastError(); F.cells_refused = true; return false;
+    }
+    if (cudaMalloc(&F.cells, bytes) != cudaSuccess) { cudaGetLastError(); F.cells = nullptr; F.cells_refused = true; return false; }
+    int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)148 * 16);
+    build_cells_kernel<<<blocks, 256, 0, st>>>(F.lin, F.cells, F.P.W, F.P.H, F.P.D);
+    if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+        cudaGetLastError(); cudaFree(F.cells); F.cells = nullptr; F.cells_refused = true; return false;
+    }
+    VLOG("field %s: per-cell polynomial table, %.1f GiB\n", F.path.c_str(), (double)bytes / 1073741824.0);
+    return true;
+}
+
 DeviceField *get_field(const char *path, int device, cudaStream_t st) {
     struct stat sb;
     long long mt = 0, fs = 0;
@@ -303,6 +329,7 @@ struct photon_scene {
     double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
     int *d_order = nullptr;              // processing order of the source points (Morton order of x, y), or null
     bool coherent = false;               // rays of a source point stay within ~a cell of each other: v5 hot loop
+    bool use_cells = false;              // ... and the field has its per-cell polynomial table (PHOTON_CELLS, default on)
     long long n_dots = 0, rays_per_dot = 0;
 };
 
@@ -377,7 +404,11 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->d_fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (s->d_fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (dump && s->use_cells) { LinearFieldCells C; static_cast<LinearField &>(C) = S; C.cells = s->field->cells;
+            trace_rays_kernel<true, 2, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, C); }   // the per-ray parity channel of the timed loop
         else if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (s->use_cells && s->occupancy == 3) { LinearFieldCells C; static_cast<LinearField &>(C) = S; C.cells = s->field->cells;
+            trace_rays_kernel<false, 3, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, C); }
         else if (s->coherent && s->occupancy == 5) { LinearFieldCoherent C; static_cast<LinearField &>(C) = S;
             trace_rays_kernel<false, 5, LinearFieldCoherent, false, 128><<<grid, 128, 0, s->stream>>>(a, C); }
         else if (s->coherent && s->occupancy == 3) { LinearFieldCoherent C; static_cast<LinearField &>(C) = S;
@@ -568,6 +599,8 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         // coherent rays: the cone of a source point at the lens (cone_ratio * lens_pitch) is narrower than a cell
         s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
         if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;
+        { const char *pc = getenv("PHOTON_CELLS");
+          s->use_cells = s->coherent && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }
         const char *smp = getenv("PHOTON_SAMPLER");
         s->use_texture = smp && strcmp(smp, "texture") == 0;
         if (s->use_texture && !ensure_texture(*s->field, s->stream)) return false;
