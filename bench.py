@@ -192,9 +192,11 @@ def workload_config(args, call):
                         f"thin lens f/11, diffraction 3 px, {call.num_particles} source points x {args.rays_per_point} rays",
             "rays_per_step": args.points_per_step * args.rays_per_point, "points_per_step": args.points_per_step,
             "field_bytes": 16 * args.grid ** 3, "coefficient_bytes": 4 * args.grid ** 3 if CUBIC else 0,
+            # per-cell polynomial table of the coherent hot loop (8 float4 per cell; PHOTON_CELLS=0 reads the texels instead)
+            "cell_table_bytes": 0 if (CUBIC or os.environ.get("PHOTON_CELLS") == "0") else 128 * args.grid ** 3,
             "interpolation": "cubic" if CUBIC else "linear", "rng": os.environ.get("PHOTON_RNG", "reference"),
             "sampler": os.environ.get("PHOTON_SAMPLER", "linear"),
-            "l2_policy": "field (2 GiB at 512^3) is larger than the 126 MB L2; consecutive steps trace different batches"}
+            "l2_policy": "field (2 GiB of texels + 16 GiB cell table at 512^3) is larger than the 126 MB L2; consecutive steps trace different batches"}
 
 
 _JSON_FD = None
@@ -352,7 +354,7 @@ def main():
             "roofline": {"bound": "fp32_issue", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp32_peak if fp32_peak and fp32_peak > 0 else None,
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
-                         "kernel": "trace_rays_kernel<BSplineField>" if CUBIC else "trace_rays_kernel<LinearField>", "kernel_ms": k_ms,
+                         "kernel": "trace_rays_kernel<BSplineField>" if CUBIC else "trace_rays_kernel<LinearFieldCells>", "kernel_ms": k_ms,
                          "flop_per_ray_step": FLOP_PER_RAY_STEP, "ray_steps_per_launch": steps_per_launch,
                          "peak_source": "FFMA loop measured live on this GPU (photon_b200_measure_fp32_tflops); "
                                         "MEASURED_PEAKS.json has no FP32 figure",

@@ -600,7 +600,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
         if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;
         { const char *pc = getenv("PHOTON_CELLS");
-          s->use_cells = s->coherent && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }
+          s->use_cells = s->coherent && algorithm == 2 && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }   // only rk4_hot reads it
         const char *smp = getenv("PHOTON_SAMPLER");
         s->use_texture = smp && strcmp(smp, "texture") == 0;
         if (s->use_texture && !ensure_texture(*s->field, s->stream)) return false;
