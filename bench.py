@@ -36,12 +36,14 @@ CUBIC = os.environ.get("PHOTON_INTERPOLATION", "linear") == "cubic"
 FLOP_PER_RAY_STEP = 1434.0 if CUBIC else 330.0
 L1_BYTES_PER_RAY_STEP = 768.0 if CUBIC else 384.0    # linear: 3 samples x 8 texels x 16 B
 # dram__bytes_read.sum + dram__bytes_write.sum of one trace launch from the ncu --set full capture under
-# profiles/ (r3h_trace_raw_selected.txt: 16.8 MB read + 849.6 MB written, linear mode, default variant);
+# profiles/ (r3k_trace_raw_selected.txt: 44.7 MB read + 1261.6 MB written, linear mode, cell-table kernel);
 # None where no capture of this mode exists.  The writes are L2 evictions of the kernel's local-memory
-# window (1168 B of stack per thread for the out-of-line generic step and the splat footprints, 133 MB
-# resident, competing for the 126 MB L2 with the field streaming through it): 17 GB/s = 0.3 % of HBM.  The
-# algorithmic HBM bytes per launch are ~4.4 MB (source points + one flush of the 4 MiB image).
-NCU_DRAM_BYTES_PER_LAUNCH = None if CUBIC else 866407936
+# window (1184 B of stack per thread for the out-of-line generic step and the splat footprints, 135 MB
+# resident, competing for the 126 MB L2 with the field streaming through it): 31 GB/s = 0.5 % of HBM.  The
+# algorithmic HBM bytes per launch are ~4.4 MB (source points + one flush of the 4 MiB image) plus the cells
+# the rays of the batch walk through once (10 000 columns x 511 cells x 128 B = 0.65 GB if nothing were shared;
+# neighbouring points share cells and the L2 keeps them: 45 MB read).
+NCU_DRAM_BYTES_PER_LAUNCH = None if CUBIC else 1306324232
 
 
 def parse():
@@ -362,9 +364,9 @@ def main():
                          "l1_gbs_achieved": steps_per_launch * L1_BYTES_PER_RAY_STEP / (k_ms * 1e-3) / 1e9,
                          "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
                          # what ncu --set full reported for this kernel and command (not measured in this run)
-                         "ncu": {"issue_slots_busy": 0.672, "fma_pipe_busy": 0.622, "dram_throughput": 0.002,
-                                 "l1_hit_rate": 0.894, "warp_instructions_per_ray_step": 241,
-                                 "source": "profiles/r3h_trace_details.txt, r3h_trace_raw_selected.txt"} if not CUBIC else None},
+                         "ncu": {"issue_slots_busy": 0.672, "fma_pipe_busy": 0.565, "dram_throughput": 0.005,
+                                 "l1_hit_rate": 0.883, "warp_instructions_per_ray_step": 204,
+                                 "source": "profiles/r3k_trace_details.txt, r3k_trace_raw_selected.txt"} if not CUBIC else None},
         }
         if not args.no_cpu_baseline and world == 1:
             cl, kind = cpu_reference_lib()
