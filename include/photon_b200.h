@@ -32,6 +32,8 @@
  *   PHOTON_NCCL=0           PHOTON_GPUS: sum the partial images through the host instead of one ncclReduce
  *   PHOTON_STEP_SCALE=<k>   integrator step = k x smallest grid spacing (the reference has k = 1 only)
  *   PHOTON_FULL_DEPTH=1     keep more than the 1024 z-planes the reference keeps (trace.h:2037-2038)
+ *   PHOTON_CELLS=<0|1>      coherent RK4 loop reads the per-cell polynomial table (128 B per voxel) [default 1 when it fits]
+ *   PHOTON_CELLS_MAX_GIB=<g>  largest table that is built [default 40]; beyond it the loop reads the corner texels
  */
 #ifndef PHOTON_B200_H_
 #define PHOTON_B200_H_

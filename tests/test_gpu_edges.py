@@ -161,3 +161,29 @@ def test_gradient_noise_matches_oracle(cuda_lib, oracle_lib, tmp_path):
     expect = 2e-9 * (511 * 176.0 / 63) * np.sqrt(63)
     assert 0.7 * expect < dd.std() < 1.3 * expect, (dd.std(), expect)
     assert np.abs(dd[:, :2].mean(axis=0)).max() < 5 * expect / np.sqrt(both.sum())
+
+
+def test_cell_table_agrees_with_corner_texels(cuda_lib, oracle_lib, tmp_path, monkeypatch):
+    """The coherent RK4 loop reads each cell from the per-cell polynomial table; PHOTON_CELLS=0 and a
+    table that does not fit (PHOTON_CELLS_MAX_GIB=0) read the corner texels.  All three against the oracle at the
+    usual bounds; the two corner-texel routes are the same kernel and agree bit for bit."""
+    call = small_bos(tmp_path, rays_per_point=60)
+    ref = util.run_with_dumps(oracle_lib, call, dump_dir(tmp_path, "o"))
+    table = util.run_with_dumps(cuda_lib, call, dump_dir(tmp_path, "t"))
+    monkeypatch.setenv("PHOTON_CELLS", "0")
+    corners = util.run_with_dumps(cuda_lib, call, dump_dir(tmp_path, "c"))
+    monkeypatch.delenv("PHOTON_CELLS")
+    second = tmp_path / "second"                              # its own file: the refusal is remembered with the cached field
+    second.mkdir()
+    other = small_bos(second, rays_per_point=60)
+    monkeypatch.setenv("PHOTON_CELLS_MAX_GIB", "0")
+    refused = util.run_with_dumps(cuda_lib, other, dump_dir(tmp_path, "r"))
+    monkeypatch.delenv("PHOTON_CELLS_MAX_GIB")
+    for name, got in (("table", table), ("corners", corners), ("refused", refused)):
+        m = util.compare(ref, got, 10.0)
+        assert m["nan_mismatch"] == 0 and m["dpos_px"] <= util.TOL_POS_PX and m["ddir_rad"] <= util.TOL_DIR_RAD, (name, m)
+        assert m["image_rel_l2"] <= util.TOL_IMG_L2, (name, m)
+    assert np.array_equal(corners[1], refused[1]) and np.array_equal(corners[2], refused[2])
+    m = util.compare(corners, table, 10.0)
+    assert m["dpos_px"] <= util.TOL_POS_PX and m["image_rel_l2"] <= util.TOL_IMG_L2, m
+    assert not np.array_equal(corners[1], table[1])          # it really is a different evaluation order
