@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--cpu-sample-points", type=int, default=0, help="0 = auto (about 10-30 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity leg of the cpu_baseline section")
     ap.add_argument("--workdir", default=None)
     return ap.parse_args()
 
@@ -156,6 +157,40 @@ def time_cpu(call, npoints, lib, kind):
         threads = lib.photon_ref_last_threads()
     return {"seconds": secs, "wall": wall, "steps": int(steps), "rays": int(npoints * call.lightray_number_per_particle),
             "threads": int(threads)}
+
+
+def parity_at_full_size(call, lib, cpu_lib, kind, workdir, npoints=96):
+    """Parity AT THE BENCHMARK'S OWN CONFIGURATION (512^3 field, 16 GiB cell table): `npoints` source points spread over
+    the whole dot grid, every ray of them, through the reference on the host cores (ray dumps on) and through the CUDA
+    library -- its dump kernel for the per-ray figures and the non-dump kernel (the one timed above) for the image."""
+    from tests import util
+    stride = max(1, call.num_particles // npoints)
+    idx = np.arange(0, call.num_particles, stride)[:npoints]
+    sub = call.subset(idx)
+    sub.source_point_number = len(idx)
+    dirs = [os.path.join(workdir, "parity_" + t) for t in ("ref", "gpu")]
+    for d in dirs:
+        os.makedirs(d, exist_ok=True)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(1)
+    os.dup2(devnull, 1)
+    try:
+        ref = util.run_with_dumps(cpu_lib, sub, dirs[0])
+    finally:
+        os.dup2(saved, 1); os.close(devnull); os.close(saved)
+    got = util.run_with_dumps(lib, sub, dirs[1])
+    v_dump = lib.photon_b200_last_variant().decode()
+    plain = sub.run(lib)
+    v_plain = lib.photon_b200_last_variant().decode()
+    m = util.compare(ref, got, float(call.camera.pixel_pitch))
+    i0 = ref[0].astype(np.float64)
+    return {"rays": m["rays"], "dpos_px": m["dpos_px"], "dpos_px_p99": m["dpos_px_p99"], "ddir_rad": m["ddir_rad"],
+            "image_rel_l2": m["image_rel_l2"],
+            "image_rel_l2_nondump": float(np.linalg.norm(i0 - plain) / max(np.linalg.norm(i0), 1e-300)),
+            "nan_mismatch": m["nan_mismatch"], "hit_fraction": m["hit_fraction"],
+            "kernels": [v_dump, v_plain], "against": "reference (host build)" if kind == "reference" else "oracle port",
+            "sample": f"{len(idx)} source points (every {stride}th of the workload) x {call.lightray_number_per_particle} rays",
+            "bounds": {"dpos_px": 1e-3, "ddir_rad": 1e-5, "image_rel_l2": 1e-4}}
 
 
 def run_reference_arm(args):
@@ -377,6 +412,11 @@ def main():
                                     "kind": kind, "rays_per_s": r["rays"] / r["seconds"],
                                     "sample": f"first {n} source points x {args.rays_per_point} rays of the same workload "
                                               f"({r['rays']} rays, {r['steps']} ray-steps, {r['seconds']:.1f} s); field load excluded"}
+            if not args.no_parity:
+                try:
+                    line["parity"] = parity_at_full_size(call, lib, cl, kind, workdir)
+                except Exception as e:            # the headline numbers stand on their own; say why parity is absent
+                    line["parity"] = {"error": repr(e)[:300]}
         emit(line)
     scene.close()
     if world > 1:

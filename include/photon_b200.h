@@ -34,6 +34,7 @@
  *   PHOTON_FULL_DEPTH=1     keep more than the 1024 z-planes the reference keeps (trace.h:2037-2038)
  *   PHOTON_CELLS=<0|1>      coherent RK4 loop reads the per-cell polynomial table (128 B per voxel) [default 1 when it fits]
  *   PHOTON_CELLS_MAX_GIB=<g>  largest table that is built [default 40]; beyond it the loop reads the corner texels
+ *   PHOTON_NO_FIELD_CACHE=1 rebuild the density field on every call
  */
 #ifndef PHOTON_B200_H_
 #define PHOTON_B200_H_
@@ -192,8 +193,21 @@ int photon_b200_unregister_field(const char *name);
 int photon_b200_load_coefficients(const char *path, float *out, long long capacity_voxels);
 /* One field sample per point at texel coordinates xyz_texel[3n] (the convention of tex3D in
  * trace.h:1052: texel centres at +0.5, clamp addressing) -> out4[4n] = (dn/dx, dn/dy, dn/dz, n-1).
- * cubic = 0: trilinear blend of the (grad n, n-1) texels; 1: tricubic B-spline with analytic gradient. */
+ * cubic = 0: trilinear blend of the (grad n, n-1) texels with exact float weights; 1: tricubic B-spline with
+ * analytic gradient; 2: the hardware unit, tex3D<float4> on the field's texture object (the reference's sampler). */
 int photon_b200_sample_field(const char *path, int cubic, int n, const float *xyz_texel, float *out4);
+
+/* What the library keeps between calls, and how to drop it.  A density field stays resident on its device after the
+ * call that loaded it (the BOS script calls twice per run with the same file): 16 B per voxel of texels, plus 128 B
+ * per voxel when the coherent RK4 loop built its cell table, plus 4 B (cubic mode) or 16 B (texture mode) -- 18 GiB
+ * for a 512^3 field with its table.  Entries are reference counted: a field is never freed under a live scene, and a
+ * field nobody holds is dropped when another one is loaded on that device or by photon_b200_release_cache(), which
+ * also trims the library's own stream-ordered memory pools.  Returns the bytes of field data released. */
+long long photon_b200_release_cache(void);
+long long photon_b200_cache_bytes(void);           /* field bytes resident now, all devices */
+/* Which trace kernel the calling thread's last launch ran: "<integrator>/<gatherer>/<dump|image|stats>[/fixed]",
+ * e.g. "rk4/cells/image" (tests use it to prove which instantiation they compared). */
+const char *photon_b200_last_variant(void);
 
 /* FP32 FMA throughput of the device in TFLOP/s, measured with a register-resident FFMA loop
  * (the roofline denominator for the trace kernel, which is FP32-issue bound, not HBM bound). */

@@ -14,6 +14,7 @@
 #include <string.h>
 #include <sys/stat.h>
 #include <chrono>
+#include <limits>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -37,6 +38,7 @@ using namespace ph;
 namespace {
 
 thread_local std::string g_error;
+thread_local std::string g_variant;       // trace kernel variant of the last launch (photon_b200_last_variant)
 bool verbose() { static int v = getenv("PHOTON_VERBOSE") ? atoi(getenv("PHOTON_VERBOSE")) : 0; return v != 0; }
 #define VLOG(...) do { if (verbose()) { printf(__VA_ARGS__); fflush(stdout); } } while (0)
 
@@ -55,9 +57,10 @@ bool cuda_ok(cudaError_t e, const char *what, const char *file, int line) {
 // library twice per run and the reference reloads + recomputes the field each time).
 // ---------------------------------------------------------------------------------
 struct DeviceField {
-    int owner = -1;                      // the device this cache slot belongs to (never changes)
-    std::mutex mu;                       // builds of different devices run concurrently (PHOTON_GPUS)
-    int device = -1;
+    std::mutex mu;                       // held while the entry is built or one of its on-demand tables is added
+    int device = -1;                     // the device the buffers live on (never changes once set)
+    int refs = 0;                        // scenes / ingest calls holding the entry (guarded by g_field_mutex)
+    bool failed = false;                 // the build failed: waiters give up, the entry is dropped
     std::string path; long long mtime = 0, fsize = 0;
     FieldParams P{};
     f3 spacing{};
@@ -67,6 +70,10 @@ struct DeviceField {
     bool cells_refused = false;          // it did not fit; do not try again for this field
     cudaArray_t arr = nullptr;           // optional 3-D array for the texture path
     cudaTextureObject_t tex = 0;
+    size_t bytes() const {
+        const size_t n = (size_t)P.W * P.H * P.D;
+        return (lin ? n * 16 : 0) + (coef ? n * 4 : 0) + (cells ? n * 128 : 0) + (arr ? n * 16 : 0);
+    }
     void release() {
         if (device >= 0) cudaSetDevice(device);
         if (tex) cudaDestroyTextureObject(tex);
@@ -74,11 +81,16 @@ struct DeviceField {
         if (lin) cudaFree(lin);
         if (coef) cudaFree(coef);
         if (cells) cudaFree(cells);
-        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; cells = nullptr; cells_refused = false; device = -1; path.clear();
+        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; cells = nullptr; cells_refused = false;
     }
 };
+// The field cache.  An entry is keyed by (device, path, mtime, size) and REFERENCE COUNTED: every scene (and every
+// ingest call) that uses a field holds a reference until it is destroyed, so loading another file, rewriting the
+// NRRD or a concurrent call from another host thread can never free buffers a live scene still reads.  Entries
+// nobody holds stay cached (the BOS script calls the library twice per run with the same file) until another
+// field is loaded on that device or photon_b200_release_cache() is called.
 std::mutex g_field_mutex;
-std::vector<DeviceField *> g_fields;     // one cache entry per device
+std::vector<DeviceField *> g_fields;
 
 // Fields registered from memory (photon_b200_register_field): density_grad_filename "mem:<name>" resolves
 // here instead of the file system -- for synthetic fields that would otherwise make a round trip through a
@@ -231,43 +243,89 @@ bool ensure_cells(DeviceField &F, cudaStream_t st) {
     return true;
 }
 
+void put_field(DeviceField *F) {
+    if (!F) return;
+    std::lock_guard<std::mutex> lk(g_field_mutex);
+    if (F->refs > 0) F->refs--;
+}
+// Takes a reference (release it with put_field).  Builds the entry on a miss; concurrent callers of the same key
+// wait for the builder on the entry's mutex.  Entries of this device that nobody holds are dropped first, so at
+// most one idle field per device stays resident.
 DeviceField *get_field(const char *path, int device, cudaStream_t st) {
     struct stat sb;
     long long mt = 0, fs = 0;
     if (stat(path, &sb) == 0) { mt = (long long)sb.st_mtim.tv_sec * 1000000000LL + sb.st_mtim.tv_nsec; fs = (long long)sb.st_size; }
     { MemField m{}; if (find_mem_field(path, m)) { mt = m.version; fs = (long long)m.nx * m.ny * m.nz; } }
-    DeviceField *slot = nullptr;
+    const bool no_cache = getenv("PHOTON_NO_FIELD_CACHE") != nullptr;
+    DeviceField *F = nullptr;
+    bool builder = false;
+    std::vector<DeviceField *> drop;
     {
         std::lock_guard<std::mutex> lk(g_field_mutex);
-        for (auto *f : g_fields) if (f->owner == device) slot = f;
-        if (!slot) { slot = new DeviceField(); slot->owner = device; g_fields.push_back(slot); }
+        if (!no_cache)
+            for (auto *f : g_fields)
+                if (f->device == device && !f->failed && f->path == path && f->mtime == mt && f->fsize == fs) { F = f; break; }
+        if (!F) {
+            for (size_t i = 0; i < g_fields.size();) {
+                DeviceField *f = g_fields[i];
+                if (f->device == device && f->refs == 0) { drop.push_back(f); g_fields.erase(g_fields.begin() + i); } else i++;
+            }
+            F = new DeviceField();
+            F->device = device; F->path = path; F->mtime = mt; F->fsize = fs;
+            F->mu.lock();                                    // released below, after the build
+            g_fields.push_back(F);
+            builder = true;
+        }
+        F->refs++;
     }
-    std::lock_guard<std::mutex> lk(slot->mu);
-    if (slot->device == device && slot->path == path && slot->mtime == mt && slot->fsize == fs && !getenv("PHOTON_NO_FIELD_CACHE")) return slot;
-    slot->release();
-    if (!build_field(*slot, path, device, st)) { slot->release(); return nullptr; }
-    slot->mtime = mt; slot->fsize = fs;
-    return slot;
+    for (auto *f : drop) { { std::lock_guard<std::mutex> w(f->mu); f->release(); } delete f; }
+    if (builder) {
+        const bool ok = build_field(*F, path, device, st);
+        if (!ok) { F->release(); F->failed = true; }
+        F->mu.unlock();
+        if (!ok) {
+            std::lock_guard<std::mutex> lk(g_field_mutex);
+            F->refs--;
+            if (F->refs == 0) { for (size_t i = 0; i < g_fields.size(); i++) if (g_fields[i] == F) { g_fields.erase(g_fields.begin() + i); break; } delete F; }
+            return nullptr;
+        }
+        return F;
+    }
+    bool failed;
+    { std::lock_guard<std::mutex> w(F->mu); failed = F->failed; }       // wait for the builder
+    if (failed) {
+        std::lock_guard<std::mutex> lk(g_field_mutex);
+        F->refs--;
+        if (F->refs == 0) { for (size_t i = 0; i < g_fields.size(); i++) if (g_fields[i] == F) { g_fields.erase(g_fields.begin() + i); break; } delete F; }
+        return nullptr;
+    }
+    return F;
 }
 
-// Per-call buffers come from the device's stream-ordered memory pool, which is told to keep what is
-// freed (release threshold = max): after the first call a scene costs no cudaMalloc/cudaFree.
-void keep_pool_memory(int device) {
-    static std::mutex m; static std::vector<int> done;
-    std::lock_guard<std::mutex> lk(m);
-    for (int d : done) if (d == device) return;
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+// Per-call buffers come from a stream-ordered memory pool of the LIBRARY'S OWN (one per device, release threshold =
+// max: after the first call a scene costs no cudaMalloc/cudaFree).  The device's default pool, which PyTorch / CuPy
+// cudaMallocAsync users of the same process share, is left alone.  photon_b200_release_cache() trims it.
+std::mutex g_pool_mutex;
+std::vector<std::pair<int, cudaMemPool_t>> g_pools;
+cudaMemPool_t device_pool(int device) {
+    std::lock_guard<std::mutex> lk(g_pool_mutex);
+    for (auto &e : g_pools) if (e.first == device) return e.second;
+    cudaMemPool_t pool = nullptr;
+    cudaMemPoolProps props; memset(&props, 0, sizeof props);
+    props.allocType = cudaMemAllocationTypePinned; props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice; props.location.id = device;
+    if (cudaMemPoolCreate(&pool, &props) == cudaSuccess) {
         unsigned long long thr = ~0ull;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-    }
-    cudaGetLastError();
-    done.push_back(device);
+    } else { cudaGetLastError(); pool = nullptr; }          // fall back to plain cudaMallocAsync
+    g_pools.emplace_back(device, pool);
+    return pool;
 }
 template <class T>
-bool pool_alloc(T *&dst, size_t bytes, cudaStream_t st) {
+bool pool_alloc(T *&dst, size_t bytes, cudaStream_t st, cudaMemPool_t pool) {
     dst = nullptr;
-    CK(cudaMallocAsync((void **)&dst, bytes ? bytes : 1, st));
+    if (pool) CK(cudaMallocFromPoolAsync((void **)&dst, bytes ? bytes : 1, pool, st));
+    else CK(cudaMallocAsync((void **)&dst, bytes ? bytes : 1, st));
     return true;
 }
 template <class T>
@@ -290,10 +348,10 @@ struct PinnedStage {
 thread_local PinnedStage g_stage;
 
 template <class T>
-bool upload(T *&dst, const T *src, size_t n, cudaStream_t st) {
+bool upload(T *&dst, const T *src, size_t n, cudaStream_t st, cudaMemPool_t pool) {
     dst = nullptr;
     if (n == 0) return true;
-    if (!pool_alloc(dst, n * sizeof(T), st)) return false;
+    if (!pool_alloc(dst, n * sizeof(T), st, pool)) return false;
     CK(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
     return true;
 }
@@ -306,6 +364,7 @@ bool upload(T *&dst, const T *src, size_t n, cudaStream_t st) {
 struct photon_scene {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaMemPool_t pool = nullptr;        // the library's own stream-ordered pool of this device
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     TraceArgs args{};
     DeviceField *field = nullptr;
@@ -388,37 +447,75 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         g_error = "dot statistics are not available together with ray dumps, PHOTON_DETERMINISTIC or PHOTON_SAMPLER=texture"; return false; }
     if (s->use_texture && s->d_fixed) { g_error = "PHOTON_DETERMINISTIC is not available with PHOTON_SAMPLER=texture"; return false; }
     if (s->use_cubic && s->d_fixed) { g_error = "PHOTON_DETERMINISTIC is not available with PHOTON_INTERPOLATION=cubic"; return false; }
-    if (s->use_cubic) {
+    // Dump launches (the per-ray parity channel) run the SAME gatherer as the non-dump launch of the scene: cell table,
+    // coherent corner texels or fan-out corner texels.  g_variant names what ran (photon_b200_last_variant).
+    const char *mode = dump ? "dump" : stats ? "stats" : "image";
+    const char *alg = a.algorithm == 1 ? "euler" : a.algorithm == 2 ? "rk4" : a.algorithm == 3 ? "rk45" : a.algorithm == 4 ? "ab4" : "?";
+    const char *gat = "none";
+    const bool slow_alg = a.simulate_gradients && (a.algorithm == 3 || a.algorithm == 4);
+    if (slow_alg && stats) { g_error = "dot statistics are not available with the rk45 / adams-bashforth integrators"; return false; }
+    if (slow_alg) {
+        // rk45 / adams-bashforth (trace.h:304-718, 1293-1453): literal restatements on the generic samplers, in kernel
+        // instantiations of their own so that their stack frames stay out of the RK4 / Euler kernels
+        gat = s->use_cubic ? "cubic" : s->use_texture ? "texture" : "generic";
+        LinearField S; S.g = s->field ? s->field->lin : nullptr; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
+        if (s->use_cubic) {
+            BSplineField B; B.c = s->field->coef; B.W = a.field.W; B.H = a.field.H; B.D = a.field.D;
+            B.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
+            if (dump) trace_rays_kernel<true, 2, BSplineField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, B);
+            else trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, B);
+        } else if (s->use_texture) {
+            TextureField T; T.tex = s->field->tex;
+            if (dump) trace_rays_kernel<true, 2, TextureField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, T);
+            else trace_rays_kernel<false, 2, TextureField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, T);
+        } else if (s->d_fixed) {
+            if (dump) trace_rays_kernel<true, 2, LinearField, true, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+            else trace_rays_kernel<false, 2, LinearField, true, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        } else {
+            if (dump) trace_rays_kernel<true, 2, LinearField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+            else trace_rays_kernel<false, 2, LinearField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        }
+    } else if (s->use_cubic) {
+        gat = "cubic";
         BSplineField S; S.c = s->field->coef; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         S.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
         if (stats) trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump) trace_rays_kernel<true, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     } else if (s->use_texture) {
+        gat = "texture";
         TextureField S; S.tex = s->field->tex;
         if (dump) trace_rays_kernel<true, 2, TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, TextureField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     } else {
         LinearField S; S.g = s->field ? s->field->lin : nullptr;
         S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
+        LinearFieldCells SC; static_cast<LinearField &>(SC) = S; SC.cells = s->use_cells ? s->field->cells : nullptr;
+        LinearFieldCoherent SH; static_cast<LinearField &>(SH) = S;
+        const bool fixed = s->d_fixed != nullptr;
+        // the gatherer of the scene (what the non-dump launch runs; PHOTON_OCC variants exist for some only)
+        enum { G_FANOUT, G_COHERENT, G_CELLS };
+        const int occ = s->occupancy;
+        int g = (stats || fixed || !a.simulate_gradients) ? G_FANOUT : s->use_cells ? G_CELLS : s->coherent ? G_COHERENT : G_FANOUT;
+        if (g == G_CELLS && occ != 3) g = G_COHERENT;
+        if (g == G_COHERENT && occ != 3 && occ != 5) g = G_FANOUT;
+        gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : "fanout";
         if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (s->d_fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (s->d_fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (dump && s->use_cells) { LinearFieldCells C; static_cast<LinearField &>(C) = S; C.cells = s->field->cells;
-            trace_rays_kernel<true, 2, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, C); }   // the per-ray parity channel of the timed loop
+        else if (fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (dump && g == G_CELLS) trace_rays_kernel<true, 2, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, SC);
+        else if (dump && g == G_COHERENT) trace_rays_kernel<true, 2, LinearFieldCoherent><<<grid, PH_BLOCK, 0, s->stream>>>(a, SH);
         else if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (s->use_cells && s->occupancy == 3) { LinearFieldCells C; static_cast<LinearField &>(C) = S; C.cells = s->field->cells;
-            trace_rays_kernel<false, 3, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, C); }
-        else if (s->coherent && s->occupancy == 5) { LinearFieldCoherent C; static_cast<LinearField &>(C) = S;
-            trace_rays_kernel<false, 5, LinearFieldCoherent, false, 128><<<grid, 128, 0, s->stream>>>(a, C); }
-        else if (s->coherent && s->occupancy == 3) { LinearFieldCoherent C; static_cast<LinearField &>(C) = S;
-            trace_rays_kernel<false, 3, LinearFieldCoherent><<<grid, PH_BLOCK, 0, s->stream>>>(a, C); }
-        else if (s->occupancy == 5) trace_rays_kernel<false, 5, LinearField, false, 128><<<grid, 128, 0, s->stream>>>(a, S);   // 96 regs, 20 warps/SM
-        else if (s->occupancy == 6) trace_rays_kernel<false, 3, LinearField, false, 192><<<grid, 192, 0, s->stream>>>(a, S);   // 112 regs, 18 warps/SM
-        else if (s->occupancy == 4) trace_rays_kernel<false, 4, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (s->occupancy == 3) trace_rays_kernel<false, 3, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (g == G_CELLS) trace_rays_kernel<false, 3, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, SC);
+        else if (g == G_COHERENT && occ == 5) trace_rays_kernel<false, 5, LinearFieldCoherent, false, 128><<<grid, 128, 0, s->stream>>>(a, SH);
+        else if (g == G_COHERENT) trace_rays_kernel<false, 3, LinearFieldCoherent><<<grid, PH_BLOCK, 0, s->stream>>>(a, SH);
+        else if (occ == 5) trace_rays_kernel<false, 5, LinearField, false, 128><<<grid, 128, 0, s->stream>>>(a, S);   // 96 regs, 20 warps/SM
+        else if (occ == 6) trace_rays_kernel<false, 3, LinearField, false, 192><<<grid, 192, 0, s->stream>>>(a, S);   // 112 regs, 18 warps/SM
+        else if (occ == 4) trace_rays_kernel<false, 4, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (occ == 3) trace_rays_kernel<false, 3, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     }
+    g_variant = std::string(a.simulate_gradients ? alg : "nofield") + "/" + gat + "/" + mode + (s->d_fixed ? "/fixed" : "");
     CK(cudaGetLastError());
     s->last_launches++; s->total_launches++;
     s->rays_traced += (long long)point_count * a.rpp;
@@ -527,7 +624,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
                        int algorithm, bool add_pos_noise, float pos_noise_std, bool add_ngrad_noise,
                        float ngrad_noise_std, float cone_ratio, int shard_index, int shard_count) {
     CK(cudaSetDevice(s->device));
-    keep_pool_memory(s->device);
+    s->pool = device_pool(s->device);
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
@@ -543,29 +640,30 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
     s->total_points = np; s->point_offset = (int)b; s->npoints = (int)(e - b);
     s->source_point_number = src->source_point_number;
     size_t n = (size_t)s->npoints;
-    if (!upload(s->d_sx, src->x + b, n, s->stream) || !upload(s->d_sy, src->y + b, n, s->stream) ||
-        !upload(s->d_sz, src->z + b, n, s->stream) || !upload(s->d_srad, src->radiance + b, n, s->stream) ||
-        !upload(s->d_sdiam, src->diameter_index + b, n, s->stream)) return false;
+    if (!upload(s->d_sx, src->x + b, n, s->stream, s->pool) || !upload(s->d_sy, src->y + b, n, s->stream, s->pool) ||
+        !upload(s->d_sz, src->z + b, n, s->stream, s->pool) || !upload(s->d_srad, src->radiance + b, n, s->stream, s->pool) ||
+        !upload(s->d_sdiam, src->diameter_index + b, n, s->stream, s->pool)) return false;
     a.sx = s->d_sx; a.sy = s->d_sy; a.sz = s->d_sz; a.sradiance = s->d_srad; a.sdiam = s->d_sdiam;
     a.rpp = rpp; a.global_point_offset = s->point_offset;
     // Processing order (north-star (b): Morton-ordered rays): consecutive CTAs take source points that are
     // neighbours in (x, y), so the field columns they march through share texels in L1/L2 whatever order the
     // caller generated the points in (random PIV particles: +7 % on C4).  Ray ids, dumps and dot statistics keep
     // the caller's order -- only the point a CTA picks changes -- and dump launches use the identity order.
+    std::vector<int> order;              // lives until the stream is synchronised at the end of this function
     {
         const char *mo = getenv("PHOTON_MORTON");
         const bool want = mo ? atoi(mo) != 0 : simulate_density_gradients;
         if (want && n > 1) {
-            std::vector<int> order = morton_order(src->x + b, src->y + b, n);
-            if (!upload(s->d_order, order.data(), n, s->stream)) return false;
+            order = morton_order(src->x + b, src->y + b, n);
+            if (!upload(s->d_order, order.data(), n, s->stream, s->pool)) return false;
         }
     }
 
     // ---- Mie table : prt.cu:3192-3210
     a.mie.enabled = strcmp(scattering_type_str, "mie") == 0;
     if (a.mie.enabled) {
-        if (!upload(s->d_angle, sc->scattering_angle, (size_t)sc->num_angles, s->stream) ||
-            !upload(s->d_irr, sc->scattering_irradiance, (size_t)sc->num_angles * sc->num_diameters, s->stream)) return false;
+        if (!upload(s->d_angle, sc->scattering_angle, (size_t)sc->num_angles, s->stream, s->pool) ||
+            !upload(s->d_irr, sc->scattering_irradiance, (size_t)sc->num_angles * sc->num_diameters, s->stream, s->pool)) return false;
         memcpy(a.mie.inv_rot, sc->inverse_rotation_matrix, sizeof a.mie.inv_rot);
         memcpy(a.mie.beam, sc->beam_propagation_vector, sizeof a.mie.beam);
         a.mie.angle = s->d_angle; a.mie.irradiance = s->d_irr;
@@ -579,7 +677,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
                          algorithm, add_pos_noise, pos_noise_std, add_ngrad_noise, ngrad_noise_std, cone_ratio, g_error))
         return false;
     if (!a.philox) {
-        if (!upload(s->d_aim, aim.data(), aim.size(), s->stream)) return false;
+        if (!upload(s->d_aim, aim.data(), aim.size(), s->stream, s->pool)) return false;
         CK(cudaStreamSynchronize(s->stream));    // aim is a local buffer
         a.aim = s->d_aim;
     }
@@ -599,6 +697,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         // coherent rays: the cone of a source point at the lens (cone_ratio * lens_pitch) is narrower than a cell
         s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
         if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;
+        std::lock_guard<std::mutex> field_lock(s->field->mu);            // the on-demand tables below are added under it
         { const char *pc = getenv("PHOTON_CELLS");
           s->use_cells = s->coherent && algorithm == 2 && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }   // only rk4_hot reads it
         const char *smp = getenv("PHOTON_SAMPLER");
@@ -617,9 +716,9 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
     }
 
     // ---- image + counters
-    if (!pool_alloc(s->d_image, (size_t)c.nx * c.ny * sizeof(float), s->stream)) return false;
+    if (!pool_alloc(s->d_image, (size_t)c.nx * c.ny * sizeof(float), s->stream, s->pool)) return false;
     CK(cudaMemsetAsync(s->d_image, 0, (size_t)c.nx * c.ny * sizeof(float), s->stream));
-    if (!pool_alloc(s->d_counters, 2 * sizeof(unsigned long long), s->stream)) return false;
+    if (!pool_alloc(s->d_counters, 2 * sizeof(unsigned long long), s->stream, s->pool)) return false;
     if (getenv("PHOTON_DETERMINISTIC") && atoi(getenv("PHOTON_DETERMINISTIC")) != 0) {
         // Upper bound of the radiance one ray can deposit in one pixel, times ALL rays of the call
         // (not of the shard: every shard must use the same scale), must stay below 2^62.
@@ -638,7 +737,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         if (bound > 0 && std::isfinite(bound)) frexp(bound, &e);
         s->fixed_scale = ldexp(1.0, 62 - e - 1);
         size_t nb = (size_t)c.nx * c.ny * sizeof(unsigned long long);
-        if (!pool_alloc(s->d_fixed, nb, s->stream)) return false;
+        if (!pool_alloc(s->d_fixed, nb, s->stream, s->pool)) return false;
         CK(cudaMemsetAsync(s->d_fixed, 0, nb, s->stream));
     }
     a.image_fixed = s->d_fixed; a.fixed_scale = s->fixed_scale;
@@ -698,7 +797,8 @@ void photon_scene_destroy(photon_scene *s) {
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->stream) cudaStreamDestroy(s->stream);
-    delete s;   // the field stays in the per-device cache
+    put_field(s->field);   // the field stays cached until another one is loaded on this device or the cache is released
+    delete s;
 }
 
 static bool scene_ok(photon_scene *s) { if (!s) { g_error = "null scene"; return false; } return cudaSetDevice(s->device) == cudaSuccess; }
@@ -712,12 +812,15 @@ int photon_scene_zero_image(photon_scene *s) {
 int photon_scene_upload_image(photon_scene *s, const float *h) {
     if (!scene_ok(s)) return 1;
     const size_t bytes = (size_t)s->args.cam.nx * s->args.cam.ny * sizeof(float);
-    const void *src = h;
-    if (void *stage = g_stage.get(bytes)) {           // pinned staging; the copy below is then truly asynchronous
-        if (!cuda_ok(cudaStreamSynchronize(s->stream), "sync", __FILE__, __LINE__)) return 1;   // staging buffer is reused
-        memcpy(stage, h, bytes); src = stage;
+    // Through the thread's pinned staging buffer (DMA at full PCIe rate instead of the driver's pageable path).  The
+    // buffer is shared by every scene this thread touches, so the copy is waited for before the call returns: no
+    // other scene can overwrite the buffer while this copy is in flight.
+    if (void *stage = g_stage.get(bytes)) {
+        memcpy(stage, h, bytes);
+        if (!cuda_ok(cudaMemcpyAsync(s->d_image, stage, bytes, cudaMemcpyHostToDevice, s->stream), "image H2D", __FILE__, __LINE__)) return 1;
+        return cuda_ok(cudaStreamSynchronize(s->stream), "image H2D", __FILE__, __LINE__) ? 0 : 1;
     }
-    return cuda_ok(cudaMemcpyAsync(s->d_image, src, bytes, cudaMemcpyHostToDevice, s->stream), "image H2D", __FILE__, __LINE__) ? 0 : 1;
+    return cuda_ok(cudaMemcpyAsync(s->d_image, h, bytes, cudaMemcpyHostToDevice, s->stream), "image H2D", __FILE__, __LINE__) ? 0 : 1;
 }
 static bool fold_fixed(photon_scene *s) {
     if (!s->d_fixed) return true;
@@ -751,8 +854,8 @@ int photon_scene_export_u16(photon_scene *s, float pixel_gain, int pixel_bit_dep
     if (!fold_fixed(s)) return 1;
     const size_t n = (size_t)s->args.cam.nx * s->args.cam.ny;
     float *tmp = nullptr; unsigned short *d16 = nullptr; unsigned int *dmax = nullptr;
-    bool ok = pool_alloc(tmp, n * sizeof(float), s->stream) && pool_alloc(d16, n * sizeof(unsigned short), s->stream) &&
-              pool_alloc(dmax, sizeof(unsigned int), s->stream);
+    bool ok = pool_alloc(tmp, n * sizeof(float), s->stream, s->pool) && pool_alloc(d16, n * sizeof(unsigned short), s->stream, s->pool) &&
+              pool_alloc(dmax, sizeof(unsigned int), s->stream, s->pool);
     if (ok) {
         const float gain = (float)std::pow(10.0, (double)pixel_gain / 20.0);
         const float levels = (float)((1 << pixel_bit_depth) - 1);
@@ -856,7 +959,7 @@ int photon_scene_enable_dot_stats(photon_scene *s, long long rays_per_dot) {
     const long long rays = (long long)s->npoints * s->args.rpp;
     const long long n = (rays + rays_per_dot - 1) / rays_per_dot;
     if (s->d_dots) { pool_free(s->d_dots, s->stream); s->d_dots = nullptr; }
-    if (!pool_alloc(s->d_dots, (size_t)n * 8 * sizeof(double), s->stream)) return 1;
+    if (!pool_alloc(s->d_dots, (size_t)n * 8 * sizeof(double), s->stream, s->pool)) return 1;
     s->n_dots = n; s->rays_per_dot = rays_per_dot;
     return cuda_ok(cudaMemsetAsync(s->d_dots, 0, (size_t)n * 8 * sizeof(double), s->stream), "dot stats", __FILE__, __LINE__) ? 0 : 1;
 }
@@ -900,6 +1003,7 @@ int photon_b200_load_field(const char *path, float meta16[16], float *out, long 
         if (out && capacity_voxels >= (long long)n)
             rc = cudaMemcpy(out, F->lin, n * sizeof(f4), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
     }
+    put_field(F);
     cudaStreamDestroy(st);
     return rc;
 }
@@ -913,12 +1017,15 @@ int photon_b200_load_coefficients(const char *path, float *out, long long capaci
     if (cudaStreamCreate(&st) != cudaSuccess) return 1;
     DeviceField *F = get_field(path, dev, st);
     int rc = 1;
-    if (F && ensure_coefficients(*F, st)) {
+    bool have = false;
+    if (F) { std::lock_guard<std::mutex> lk(F->mu); have = ensure_coefficients(*F, st); }
+    if (have) {
         size_t n = (size_t)F->P.W * F->P.H * F->P.D;
         rc = 0;
         if (out && capacity_voxels >= (long long)n)
             rc = cudaMemcpy(out, F->coef, n * sizeof(float), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
     }
+    put_field(F);
     cudaStreamDestroy(st);
     return rc;
 }
@@ -934,12 +1041,17 @@ int photon_b200_sample_field(const char *path, int cubic, int n, const float *xy
     DeviceField *F = get_field(path, dev, st);
     int rc = 1;
     float *d_in = nullptr, *d_out = nullptr;
-    if (F && (!cubic || ensure_coefficients(*F, st)) &&
+    bool have = F != nullptr;
+    if (have && cubic) { std::lock_guard<std::mutex> lk(F->mu); have = cubic == 2 ? ensure_texture(*F, st) : ensure_coefficients(*F, st); }
+    if (have &&
         cudaMalloc(&d_in, (size_t)n * 3 * sizeof(float)) == cudaSuccess &&
         cudaMalloc(&d_out, (size_t)n * 4 * sizeof(float)) == cudaSuccess &&
         cudaMemcpyAsync(d_in, xyz_texel, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, st) == cudaSuccess) {
         int blocks = (n + 127) / 128;
-        if (cubic) {
+        if (cubic == 2) {
+            TextureField S; S.tex = F->tex;
+            sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
+        } else if (cubic) {
             BSplineField S; S.c = F->coef; S.W = F->P.W; S.H = F->P.H; S.D = F->P.D;
             S.inv_sp = mk3(1.0f / F->spacing.x, 1.0f / F->spacing.y, 1.0f / F->spacing.z);
             sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
@@ -953,9 +1065,40 @@ int photon_b200_sample_field(const char *path, int cubic, int n, const float *xy
     }
     if (rc) { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && g_error.empty()) g_error = cudaGetErrorString(e); }
     cudaFree(d_in); cudaFree(d_out);
+    put_field(F);
     cudaStreamDestroy(st);
     return rc;
 }
+
+// Drop what the library keeps between calls: every cached density field nobody is using (texels, cell table,
+// spline coefficients, texture array -- 18 GiB per device for a 512^3 field with its cell table) and the memory
+// its stream-ordered pools hold.  Fields of live scenes stay.  Returns the number of bytes of field data released.
+long long photon_b200_release_cache(void) {
+    std::vector<DeviceField *> drop;
+    {
+        std::lock_guard<std::mutex> lk(g_field_mutex);
+        for (size_t i = 0; i < g_fields.size();) {
+            if (g_fields[i]->refs == 0) { drop.push_back(g_fields[i]); g_fields.erase(g_fields.begin() + i); } else i++;
+        }
+    }
+    long long freed = 0;
+    for (auto *f : drop) { { std::lock_guard<std::mutex> w(f->mu); freed += (long long)f->bytes(); f->release(); } delete f; }
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mutex);
+        for (auto &e : g_pools) if (e.second) { cudaSetDevice(e.first); cudaDeviceSynchronize(); cudaMemPoolTrimTo(e.second, 0); }
+    }
+    cudaGetLastError();
+    return freed;
+}
+// Bytes of field data currently resident in the cache, over all devices (held or idle).
+long long photon_b200_cache_bytes(void) {
+    std::lock_guard<std::mutex> lk(g_field_mutex);
+    long long b = 0;
+    for (auto *f : g_fields) b += (long long)f->bytes();
+    return b;
+}
+// Which trace kernel the last launch of this host thread ran, e.g. "rk4/cells/dump" (tests assert on it).
+const char *photon_b200_last_variant(void) { return g_variant.c_str(); }
 
 }  // extern "C"
 
@@ -970,7 +1113,7 @@ bool write_f3_file(const std::string &dir, const char *prefix, int k, const floa
     std::string path = dir + name;
     FILE *f = fopen(path.c_str(), "wb");
     if (!f) { fprintf(stderr, "libparallel_ray_tracing(b200): cannot write %s\n", path.c_str()); return false; }
-    fwrite(data, 3 * sizeof(float), count_f3, f);
+    if (count_f3) fwrite(data, 3 * sizeof(float), count_f3, f);
     fclose(f);
     return true;
 }
@@ -1022,9 +1165,11 @@ struct NcclApi {
 NcclApi g_nccl;
 // Sum the shard images onto scene 0 of device 0.  float mode: ncclFloat sum of the images; deterministic mode:
 // ncclUint64 sum of the fixed-point images (exact, order-free), folded into the float image once on device 0.
-bool nccl_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
+// Returns 0 = reduced, 1 = NCCL not available (nothing was enqueued: the caller may sum through the host),
+// 2 = failed after the reduce was enqueued (device 0's image may be partly reduced: the caller must give up).
+int nccl_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
     std::lock_guard<std::mutex> lk(g_nccl.mu);
-    if (!g_nccl.ensure(n)) return false;
+    if (!g_nccl.ensure(n)) return 1;
     const bool fixed = res[0].scene->d_fixed != nullptr;
     ncclResult_t r = g_nccl.GroupStart();
     for (int g = 0; g < n && r == ncclSuccess; g++) {
@@ -1035,12 +1180,12 @@ bool nccl_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
     }
     ncclResult_t e = g_nccl.GroupEnd();
     if (r == ncclSuccess) r = e;
-    if (r != ncclSuccess) { fprintf(stderr, "libparallel_ray_tracing(b200): ncclReduce: %s\n", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"); return false; }
-    for (int g = 0; g < n; g++) { cudaSetDevice(res[g].scene->device); if (cudaStreamSynchronize(res[g].scene->stream) != cudaSuccess) return false; }
-    return true;
+    if (r != ncclSuccess) { fprintf(stderr, "libparallel_ray_tracing(b200): ncclReduce: %s\n", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"); return 2; }
+    for (int g = 0; g < n; g++) { cudaSetDevice(res[g].scene->device); if (cudaStreamSynchronize(res[g].scene->stream) != cudaSuccess) { cudaGetLastError(); return 2; } }
+    return 0;
 }
 #else
-bool nccl_reduce_images(std::vector<ShardResult> &, int, size_t) { return false; }
+int nccl_reduce_images(std::vector<ShardResult> &, int, size_t) { return 1; }
 #endif
 
 }  // namespace
@@ -1073,6 +1218,7 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
     int ngpus = 1;
     if (const char *g = getenv("PHOTON_GPUS")) ngpus = std::max(1, std::min(atoi(g), photon_b200_device_count()));
     const bool dumps = save_lightrays && num_lightrays_save > 0;
+    const bool empty_dump_files = save_lightrays && num_lightrays_save <= 0;     // the reference writes empty files then
     const bool inter = simulate_density_gradients && save_intermediate_ray_data && num_intermediate_positions_save > 0 && num_lightrays_save > 0;
     if (dumps || inter) ngpus = 1;       // dump files are per batch of the whole point list
     const size_t npix = (size_t)camera_design_p->x_pixel_number * camera_design_p->y_pixel_number;
@@ -1100,12 +1246,15 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
         lap("scene create");
         bool ok = photon_scene_upload_image(s, image_array) == 0;        // accumulate onto the caller's image (prt.cu:3309)
         lap("image H2D");
+        // batches of the points THIS scene holds (all of them, or the PHOTON_SHARD range): prt.cu:3506-3510
+        const int held = photon_scene_num_points(s);
+        const int spn = std::min(lightfield_source_p->source_point_number, held);
+        const int kmax = spn > 0 ? (held + spn - 1) / spn : 0;
         if (ok && (dumps || inter)) {
-            int spn = std::min(lightfield_source_p->source_point_number, np);
-            int kmax = spn > 0 ? (np + spn - 1) / spn : 0;               // prt.cu:3506-3510
             size_t ns = (size_t)std::max(num_lightrays_save, 0);
-            std::vector<float> fpos(3 * ns), fdir(3 * ns), ipos, idir;
-            if (inter) { ipos.resize(3 * ns * num_intermediate_positions_save); idir.resize(ipos.size()); }
+            const float qnan = std::numeric_limits<float>::quiet_NaN();
+            std::vector<float> fpos(3 * ns, qnan), fdir(3 * ns, qnan), ipos, idir;   // prt.cu:3527-3533
+            if (inter) { ipos.assign(3 * ns * num_intermediate_positions_save, qnan); idir.assign(ipos.size(), qnan); }
             for (int k = 0; k < kmax && ok; k++) {
                 VLOG("%d out of %d\n", k + 1, kmax);
                 ok = photon_scene_trace_batch(s, k, (long long)ns, fpos.data(), fdir.data(),
@@ -1122,6 +1271,10 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
             }
         } else if (ok) {
             ok = photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
+            for (int k = 0; k < kmax && ok && empty_dump_files; k++) {    // save_lightrays with nothing to save: empty files
+                write_f3_file(lightray_position_save_path, "pos_", k, nullptr, 0);
+                write_f3_file(lightray_direction_save_path, "dir_", k, nullptr, 0);
+            }
         }
         lap("trace");
         if (ok) {
@@ -1153,10 +1306,16 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
     auto destroy_all = [&]() { for (int g = 0; g < ngpus; g++) if (res[g].scene) photon_scene_destroy(res[g].scene); };
     if (!all_ok) { destroy_all(); return; }
     lap("trace (all GPUs)");
-    if (nccl_reduce_images(res, ngpus, npix)) {                       // one reduce over NVLink, then one D2H
+    const int red = nccl_reduce_images(res, ngpus, npix);             // one reduce over NVLink, then one D2H
+    if (red == 0) {
         lap("nccl reduce");
         photon_scene_download_image(res[0].scene, image_array);      // folds the fixed-point sum first, if any
         lap("image D2H");
+        destroy_all();
+        return;
+    }
+    if (red == 2) {                                                   // device 0 may hold a partly reduced image: no second sum
+        fprintf(stderr, "libparallel_ray_tracing(b200): image reduce failed; image untouched\n");
         destroy_all();
         return;
     }

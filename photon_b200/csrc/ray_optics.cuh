@@ -129,61 +129,91 @@ PH_HD double cos4_alpha(f3 d) {                                         // prt.c
     return (double)(c * c * c * c);
 }
 
-// Separable erf-Gaussian footprint of one ray (prt.cu:1466-1540).  The reference
-// evaluates 4 erf per rendered pixel; ex depends only on the column and ey only on
-// the row, so evaluating them once per column/row gives bit-identical increments with
-// ~4x fewer erf calls.  PH_SPLAT_MAX bounds the footprint (ceil(1.5 D)+2 columns).
-#define PH_SPLAT_MAX 16
+// Separable erf-Gaussian footprint of one ray (prt.cu:1466-1540).  The reference evaluates 4 erf per rendered
+// pixel; the column factor depends only on the column and the row factor only on the row, so evaluating them once
+// per column / row gives bit-identical increments with ~4x fewer erf calls.  The factors are never stored in an
+// indexable array: the row factors of a footprint of up to N rows live in registers (loops over them are fully
+// unrolled), the column factor is computed when its column is walked, and a footprint with more rows than the
+// largest N falls back to one pair of erf per pixel -- any diameter renders, nothing sits in local memory.
 struct ErfFootprint {
     int c0, r0, nc, nr;        // first column/row and counts (unclipped)
-    float X, Y, radius;
-    double ex[PH_SPLAT_MAX], ey[PH_SPLAT_MAX];
+    float X, Y, radius, diam;
     double scale;              // peak*pi/32
     bool valid;
 };
 
-PH_HD void erf_footprint(ErfFootprint &fp, float d_x, float d_y, double radiance, double c4,
-                         float diam, float frac) {
+PH_HD void erf_footprint(ErfFootprint &fp, float d_x, float d_y, double radiance, double c4, float diam, float frac) {
     const double pi = 3.141592653589793;
     fp.X = (float)((double)d_x - 0.5); fp.Y = (float)((double)d_y - 0.5);
     float peak = (float)(radiance * c4 * 8.0 / pi);
-    float sqrt8 = sqrtf(8.0f);
-    fp.radius = frac * diam;
+    fp.radius = frac * diam; fp.diam = diam;
     fp.c0 = (int)floorf(fp.X - fp.radius); int c1 = (int)ceilf(fp.X + fp.radius);
     fp.r0 = (int)floorf(fp.Y - fp.radius); int r1 = (int)ceilf(fp.Y + fp.radius);
     fp.nc = c1 - fp.c0 + 1; fp.nr = r1 - fp.r0 + 1;
-    fp.valid = fp.nc >= 1 && fp.nr >= 1 && fp.nc <= PH_SPLAT_MAX && fp.nr <= PH_SPLAT_MAX;
+    fp.valid = fp.nc >= 1 && fp.nr >= 1;
     fp.scale = (double)peak * pi / 32.0;
-    if (!fp.valid) return;
-#pragma unroll 1
-    for (int i = 0; i < fp.nc; i++) {
-        double u = (double)((float)(fp.c0 + i) - fp.X);
-        fp.ex[i] = erf((double)sqrt8 * (u - 0.5) / (double)diam) - erf((double)sqrt8 * (u + 0.5) / (double)diam);
-    }
-#pragma unroll 1
-    for (int i = 0; i < fp.nr; i++) {
-        double u = (double)((float)(fp.r0 + i) - fp.Y);
-        fp.ey[i] = erf((double)sqrt8 * (u - 0.5) / (double)diam) - erf((double)sqrt8 * (u + 0.5) / (double)diam);
-    }
+}
+// erf(sqrt8 (u - 1/2) / D) - erf(sqrt8 (u + 1/2) / D) at pixel index idx of the axis whose centre is c
+// (prt.cu:1516-1523; the literal 0.5 promotes to double there)
+PH_HD double erf_factor(const ErfFootprint &fp, int idx, float c) {
+    const float sqrt8 = sqrtf(8.0f);
+    const double u = (double)((float)idx - c);
+    return erf((double)sqrt8 * (u - 0.5) / (double)fp.diam) - erf((double)sqrt8 * (u + 0.5) / (double)fp.diam);
+}
+PH_HD bool erf_pixel_inside(const ErfFootprint &fp, int col, int row) {
+    const float dx = (float)col - fp.X, dy = (float)row - fp.Y;
+    return sqrtf(dx * dx + dy * dy) <= fp.radius;
 }
 
+// One ray's footprint into an accumulator; row factors of up to N rows in registers.
+template <int N, class Acc>
+PH_HD void erf_splat_rows(const ErfFootprint &fp, const Camera &cam, Acc &acc) {
+    double ey[N];
+#pragma unroll
+    for (int q = 0; q < N; q++) ey[q] = 0.0;
+#pragma unroll 1                                             // ONE inlined copy of the erf pair; the value is steered
+    for (int j = 0; j < fp.nr; j++) {                        // into its register by an unrolled select
+        const int row = fp.r0 + j;
+        if (row < 0 || row > cam.ny - 1) continue;
+        const double v = erf_factor(fp, row, fp.Y);
+#pragma unroll
+        for (int q = 0; q < N; q++) if (q == j) ey[q] = v;
+    }
+#pragma unroll 1
+    for (int i = 0; i < fp.nc; i++) {
+        const int col = fp.c0 + i;
+        if (col < 0 || col > cam.nx - 1) continue;
+        const double ex = erf_factor(fp, col, fp.X);
+#pragma unroll
+        for (int j = 0; j < N; j++) {
+            const int row = fp.r0 + j;
+            if (j >= fp.nr || row < 0 || row > cam.ny - 1) continue;
+            if (!erf_pixel_inside(fp, col, row)) continue;
+            acc.add(row, col, (float)(fp.scale * ex * ey[j]));
+        }
+    }
+}
+// Any footprint: a pair of erf per column and per pixel (large diffraction diameters; rare).
+// Arguments by value: a reference into the caller's frame would pin its footprint record in local memory.
+template <class Acc>
+PH_COLD void erf_splat_any(const ErfFootprint fp, const Camera &cam, Acc acc) {
+    for (int i = 0; i < fp.nc; i++) {
+        const int col = fp.c0 + i;
+        if (col < 0 || col > cam.nx - 1) continue;
+        const double ex = erf_factor(fp, col, fp.X);
+        for (int j = 0; j < fp.nr; j++) {
+            const int row = fp.r0 + j;
+            if (row < 0 || row > cam.ny - 1) continue;
+            if (!erf_pixel_inside(fp, col, row)) continue;
+            acc.add(row, col, (float)(fp.scale * ex * erf_factor(fp, row, fp.Y)));
+        }
+    }
+}
 template <class Acc>
 PH_HD void erf_splat(const ErfFootprint &fp, const Camera &cam, Acc &acc) {
     if (!fp.valid) return;
-    for (int i = 0; i < fp.nc; i++) {
-        int col = fp.c0 + i;
-        if (col < 0 || col > cam.nx - 1) continue;
-        float dx = (float)col - fp.X;
-        for (int j = 0; j < fp.nr; j++) {
-            int row = fp.r0 + j;
-            if (row < 0 || row > cam.ny - 1) continue;
-            float dy = (float)row - fp.Y;
-            float rr = sqrtf(dx * dx + dy * dy);
-            if (!(rr <= fp.radius)) continue;
-            float inc = (float)(fp.scale * fp.ex[i] * fp.ey[j]);
-            acc.add(row, col, inc);
-        }
-    }
+    if (fp.nr <= 8) erf_splat_rows<8>(fp, cam, acc);
+    else erf_splat_any(fp, cam, acc);
 }
 
 // pixel coordinates of a sensor hit; flip_x for the diffraction / apparent models
@@ -197,7 +227,7 @@ PH_HD bool pixel_coords(f3 hit, const Camera &cam, bool flip_x, float &d_x, floa
 
 // Bilinear 4-pixel splat (prt.cu:1810-1850 weights, 2219-2234 accumulation).  The
 // reference subtracts 1 from both indices after its bounds test; a resulting negative
-// linear index (its out-of-bounds write) is dropped.
+// linear index (its out-of-bounds write) is dropped.  Acc::add_slot(k, idx, v): k = corner 0..3.
 template <class Acc>
 PH_HD void bilinear_splat(float d_x, float d_y, double radiance, double c4, const Camera &cam, Acc &acc) {
     float yl = (float)((double)d_y - 0.5), xl = (float)((double)d_x - 0.5);
@@ -213,7 +243,7 @@ PH_HD void bilinear_splat(float d_x, float d_y, double radiance, double c4, cons
         long idx = (long)(ii - 1) * cam.nx + jj - 1;
         if (idx < 0) continue;
         float inc = (float)(w * rc * c4);
-        acc.add_linear(idx, inc);
+        acc.add_slot(k, idx, inc);
     }
 }
 

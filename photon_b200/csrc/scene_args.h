@@ -91,9 +91,8 @@ inline bool fill_scene_args(TraceArgs &a, std::vector<f2> &aim, float lens_pitch
     c.p1y = (float)((double)(-c.pitch * (float)(c.ny - 1)) / 2.0);
     a.implement_diffraction = cam->implement_diffraction ? 1 : 0;
     if (c.nx < 1 || c.ny < 1) { err = "sensor has no pixels"; return false; }
-    if (a.implement_diffraction && !(1.5f * c.diffraction_diameter + 3.0f <= (float)PH_SPLAT_MAX)) {
-        err = "diffraction_diameter too large for the splat footprint (max ~6 px)"; return false;
-    }
+    // any diffraction diameter renders (the reference has no bound either, prt.cu:1466-1540): footprints of more than
+    // 8 rows leave the register path for one pair of erf per pixel (ray_optics.cuh: erf_splat)
 
     a.image_distance = image_distance; a.wavelength = beam_wavelength;
     a.inv_fnum2 = 1 / (f_number * f_number);                             // prt.cu:233

@@ -131,7 +131,7 @@ PH_HD SensorSample ray_epilogue(const TraceArgs &a, Ray &ray, NormalStream &ns, 
     return out;
 }
 
-template <bool DUMP, class Sampler, bool STATS = false>
+template <bool DUMP, class Sampler, bool STATS = false, int ALGS = 0>
 PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr,
                                                   long long gid, bool save, unsigned long long &steps) {
     NormalStream ns;
@@ -141,7 +141,7 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
         if (DUMP && a.inter_pos && gid < a.n_save) {
             im.pos = a.inter_pos + (size_t)gid * a.n_inter; im.dir = a.inter_dir + (size_t)gid * a.n_inter; im.n = a.n_inter;
         }
-        steps += (unsigned long long)trace_volume<DUMP>(ray, a.field, S, a.algorithm, im, a.add_ngrad_noise != 0, a.ngrad_noise_std, ns);
+        steps += (unsigned long long)trace_volume<DUMP, Sampler, ALGS>(ray, a.field, S, a.algorithm, im, a.add_ngrad_noise != 0, a.ngrad_noise_std, ns);
     }
     return ray_epilogue<DUMP, STATS>(a, ray, ns, gid, save);
 }

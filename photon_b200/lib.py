@@ -76,6 +76,14 @@ def load_library(require_gpu=False):
         lib.photon_scene_reset_dot_stats.restype = C.c_int
         lib.photon_scene_download_dot_stats.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong]
         lib.photon_scene_download_dot_stats.restype = C.c_int
+        lib.photon_b200_release_cache.argtypes = []
+        lib.photon_b200_release_cache.restype = C.c_longlong
+        lib.photon_b200_cache_bytes.argtypes = []
+        lib.photon_b200_cache_bytes.restype = C.c_longlong
+        lib.photon_b200_last_variant.argtypes = []
+        lib.photon_b200_last_variant.restype = C.c_char_p
+        lib.photon_b200_sample_field.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        lib.photon_b200_sample_field.restype = C.c_int
         lib.photon_b200_measure_fp32_tflops.argtypes = [C.c_int]
         lib.photon_b200_measure_fp32_tflops.restype = C.c_double
         lib.photon_b200_measure_fp32x2_tflops.argtypes = [C.c_int]

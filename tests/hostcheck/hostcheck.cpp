@@ -21,6 +21,7 @@ struct HostAcc {
     double *img; int nx;
     void add(int row, int col, float v) { img[(size_t)row * nx + col] += (double)v; }
     void add_linear(long idx, float v) { img[idx] += (double)v; }
+    void add_slot(int, long idx, float v) { add_linear(idx, v); }
 };
 }
 

@@ -187,3 +187,65 @@ def test_cell_table_agrees_with_corner_texels(cuda_lib, oracle_lib, tmp_path, mo
     m = util.compare(corners, table, 10.0)
     assert m["dpos_px"] <= util.TOL_POS_PX and m["image_rel_l2"] <= util.TOL_IMG_L2, m
     assert not np.array_equal(corners[1], table[1])          # it really is a different evaluation order
+
+
+# ---- what the library keeps between calls (field cache) and large splat footprints ------------------------------------
+def test_field_of_a_live_scene_survives_other_loads_and_release(tmp_path, cuda_lib):
+    """Cache entries are reference counted: loading another field on the same device, or asking the library to drop
+    its cache, never frees the buffers a live scene reads.  Once the scene is gone the release returns the memory."""
+    from photon_b200.scene import ResidentScene
+    call = small_bos(tmp_path)
+    cuda_lib.photon_b200_release_cache()
+    assert cuda_lib.photon_b200_cache_bytes() == 0
+    s = ResidentScene(call)
+    s.trace(); first = s.download_image()
+    held = cuda_lib.photon_b200_cache_bytes()
+    assert held >= 16 * 64 ** 3
+    # another file on the same device while the scene is alive
+    other = os.path.join(str(tmp_path), "other.nrrd")
+    write_nrrd(other, scenes.gaussian_blob(32, 511 * 176.0 / 31, 15e3), (511 * 176.0 / 31,) * 3, (-44968.0, -44968.0, 705032.0))
+    meta = np.zeros(16, np.float32)
+    assert cuda_lib.photon_b200_load_field(other.encode(), meta.ctypes.data, None, 0) == 0
+    assert cuda_lib.photon_b200_release_cache() >= 16 * 32 ** 3          # the idle entry goes, the held one stays
+    assert cuda_lib.photon_b200_cache_bytes() == held
+    s.zero_image(); s.trace(); again = s.download_image()
+    np.testing.assert_allclose(again, first, rtol=2e-5, atol=1e-6 * float(first.max()))
+    s.close()
+    assert cuda_lib.photon_b200_release_cache() == held
+    assert cuda_lib.photon_b200_cache_bytes() == 0
+    # and the next call simply loads it again
+    assert call.run(cuda_lib).sum() > 0
+
+
+@pytest.mark.parametrize("model,diam", [("apparent", 8.0), ("general", 9.0), ("apparent", 3.0)])
+def test_large_diffraction_footprints_render(model, diam, cuda_lib, oracle_lib):
+    """Footprints wider than the register path (more than 8 rows: D > ~3.5 px, or the apparent-image model whose
+    radius is a full diameter) take the per-pixel path: nothing is dropped, the image still matches the oracle's
+    (the reference has no bound on the diameter, prt.cu:1466-1540)."""
+    c = scenes.c1_piv(particles=60, rays_per_particle=64, lens_model=model, nx=256, ny=256)
+    c.camera.diffraction_diameter = diam
+    c.camera.implement_diffraction = True
+    ref = c.run(oracle_lib)
+    got = c.run(cuda_lib)
+    assert ref.sum() > 0
+    rel = float(np.linalg.norm(got.astype(np.float64) - ref) / np.linalg.norm(ref.astype(np.float64)))
+    print(model, diam, "image rel L2:", rel)
+    assert rel <= util.TOL_IMG_L2
+
+
+def test_save_lightrays_with_nothing_to_save_writes_empty_files(tmp_path, cuda_lib):
+    """save_lightrays with num_lightrays_save = 0: the reference still writes its per-batch files, empty
+    (prt.cu:3561-3611 with n = 0)."""
+    c = small_bos(tmp_path, rays_per_point=8)
+    c.source_point_number = 100
+    d = dump_dir(tmp_path, "empty")
+    c.save_lightrays = True
+    c.num_lightrays_save = 0
+    c.lightray_position_save_path = d
+    c.lightray_direction_save_path = d
+    img = c.run(cuda_lib)
+    assert img.sum() > 0
+    nb = -(-c.num_particles // 100)
+    files = sorted(os.listdir(d))
+    assert files == sorted(["pos_%04d.bin" % k for k in range(nb)] + ["dir_%04d.bin" % k for k in range(nb)])
+    assert all(os.path.getsize(os.path.join(d, f)) == 0 for f in files)

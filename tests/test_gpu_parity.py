@@ -103,3 +103,87 @@ def test_generic_marcher_and_intermediate_dumps(name, cases, cuda_lib, oracle_li
         assert np.array_equal(np.isnan(a), np.isnan(b))
         ok = np.isfinite(a)
         assert ok.mean() > 0.5 and np.abs(a[ok] - b[ok]).max() <= tol, (kind, np.abs(a[ok] - b[ok]).max())
+
+
+# ---- the kernels the benchmark times --------------------------------------------------------------------------------
+# Ray dumps run trace_rays_kernel<DUMP = true, 128 registers>; the benchmark and every production call run the
+# non-dump instantiation (<false, 3, ...>, 80 registers, its own ptxas schedule).  Its only output is the image, so
+# the image is what is compared with the oracle's, for every scene that marches through a field.
+FIELD_CASES = ["bos_rk4_thin_diffraction", "bos_euler_thin_diffraction", "bos_rk4_multibatch_ragged",
+               "bos_rk45_thin_diffraction", "bos_ab4_thin_diffraction"]
+
+
+def _rel_l2(a, b):
+    a = a.astype(np.float64); b = b.astype(np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+@pytest.mark.parametrize("name", FIELD_CASES)
+def test_nondump_kernel_image_matches_oracle(name, cases, cuda_lib, oracle_lib):
+    call, _ = cases[name]
+    assert not call.save_lightrays
+    ref = call.run(oracle_lib)
+    got = call.run(cuda_lib)
+    variant = cuda_lib.photon_b200_last_variant().decode()
+    m = _rel_l2(got, ref)
+    print(name, variant, "image rel L2 vs oracle:", m)
+    assert variant.endswith("/image"), variant
+    assert m <= (5e-3 if name in util.AB4_CASES else util.TOL_IMG_L2), (name, variant, m)
+
+
+GATHERERS = {"cells": {}, "coherent": {"PHOTON_CELLS": "0"}, "fanout": {"PHOTON_HOT": "4"}}
+
+
+@pytest.mark.parametrize("dump", [True, False], ids=["dump", "image"])
+@pytest.mark.parametrize("gatherer", list(GATHERERS))
+def test_every_rk4_gatherer_dump_and_image(gatherer, dump, cases, cuda_lib, oracle_lib, tmp_path, monkeypatch):
+    """The three RK4 hot loops the driver can pick for a linear field -- per-cell polynomial table, coherent corner
+    texels (what a coherent scene runs when the table does not fit: C3 at 1024^3, all of C5), fan-out corner texels
+    (PIV through a field) -- each through its dump kernel (per-ray parity) and its non-dump kernel (image parity).
+    photon_b200_last_variant proves which kernel ran."""
+    call, pitch = cases["bos_rk4_thin_diffraction"]
+    for k, v in GATHERERS[gatherer].items():
+        monkeypatch.setenv(k, v)
+    (tmp_path / "o").mkdir(); (tmp_path / "g").mkdir()
+    if dump:
+        ref = util.run_with_dumps(oracle_lib, call, str(tmp_path / "o"))
+        got = util.run_with_dumps(cuda_lib, call, str(tmp_path / "g"))
+        variant = cuda_lib.photon_b200_last_variant().decode()
+        m = util.compare(ref, got, pitch)
+        print(gatherer, variant, m)
+        assert variant == "rk4/%s/dump" % gatherer, variant
+        util.assert_parity("bos_rk4_thin_diffraction", m)
+    else:
+        ref = call.run(oracle_lib)
+        got = call.run(cuda_lib)
+        variant = cuda_lib.photon_b200_last_variant().decode()
+        m = _rel_l2(got, ref)
+        print(gatherer, variant, "image rel L2 vs oracle:", m)
+        assert variant == "rk4/%s/image" % gatherer, variant
+        assert m <= util.TOL_IMG_L2, (variant, m)
+
+
+def test_c4_shaped_scene_matches_oracle(cuda_lib, oracle_lib, tmp_path):
+    """BASELINE C4's combination at test size: Mie table from bhmie, thick lens, bilinear splat, turbulent field,
+    rays that fan out over many cells (cone ratio 1) -> the fan-out gatherer, dump and non-dump kernels."""
+    from photon_b200 import scenes
+    call = scenes.c4_piv(str(tmp_path / "turb.nrrd"), n=48, particles=300, rays_per_particle=200, nx=1024, ny=1024)
+    call.source_point_number = call.num_particles
+    (tmp_path / "o").mkdir(); (tmp_path / "g").mkdir()
+    ref = util.run_with_dumps(oracle_lib, call, str(tmp_path / "o"))
+    got = util.run_with_dumps(cuda_lib, call, str(tmp_path / "g"))
+    variant = cuda_lib.photon_b200_last_variant().decode()
+    m = util.compare(ref, got, 17.0)
+    print("C4-shaped", variant, m)
+    assert variant == "rk4/fanout/dump", variant
+    util.assert_parity("piv_mie_thick_bilinear", m)                      # thick lens: 1e-3 px at the 99.9th percentile
+    plain = call.run(cuda_lib)
+    variant = cuda_lib.photon_b200_last_variant().decode()
+    assert variant == "rk4/fanout/image", variant
+    assert _rel_l2(plain, ref[0]) <= util.TOL_IMG_L2
+    # the field matters in this scene: without it the hits move
+    call.simulate_density_gradients = False
+    (tmp_path / "n").mkdir()
+    nof = util.run_with_dumps(oracle_lib, call, str(tmp_path / "n"))
+    both = np.isfinite(ref[1][:, 0]) & np.isfinite(nof[1][:, 0])
+    assert np.abs(ref[1][both] - nof[1][both])[:, :2].max() > 1e-3

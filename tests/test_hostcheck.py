@@ -56,3 +56,17 @@ def test_thick_lens_conditioning(cases, oracle_lib, tmp_path):
     assert res["bos_rk4_thin_diffraction"]["dpos_px"] <= util.TOL_POS_PX
     thick = res["piv_mie_thick_bilinear"]
     assert thick["dpos_px_p999"] <= util.TOL_POS_PX and thick["dpos_px"] <= util.THICK_LENS_MAX_PX
+
+
+@pytest.mark.parametrize("model,diam", [("apparent", 8.0), ("general", 9.0)])
+def test_large_footprints_on_the_host(model, diam, hostcheck_lib, oracle_lib):
+    """Footprints of more than 8 rows leave the register path of erf_splat (ray_optics.cuh) for one pair of erf per
+    pixel; the increments stay the oracle's (same expression, same order)."""
+    from photon_b200 import scenes
+    c = scenes.c1_piv(particles=60, rays_per_particle=64, lens_model=model, nx=256, ny=256)
+    c.camera.diffraction_diameter = diam
+    c.camera.implement_diffraction = True
+    ref = c.run(oracle_lib)
+    got = c.run(hostcheck_lib)
+    assert ref.sum() > 0
+    assert float(np.linalg.norm(got.astype(np.float64) - ref) / np.linalg.norm(ref.astype(np.float64))) <= 1e-7

@@ -92,3 +92,67 @@ def test_cuda_sample_piv_matches_reference(i, cuda_lib):
     print("sample-data/piv frame", i, "binned image rel L2 vs reference:", m)
     assert m <= util.TOL_IMG_L2
     assert abs(float(img.astype(np.float64).sum()) / float(ex["ref_sum%d" % i]) - 1) < 1e-5
+
+
+# ---- sample-data/bos/sample-parameters.mat: the shipped parameter file whose rays DO cross sample-density.nrrd -------
+# Camera turned 150 degrees about y (camera <-> volume rotation of prt.cu:2061-2076 / 2100-2111 with a non-identity
+# matrix), Euler (algorithm 1), thin lens, 512 x 512, 7225 regular dots x 100 rays.  The reference's unchanged scripts
+# wrote per-ray dumps for it (save_lightrays = 1 in the file); every 180th ray of the second call is stored.
+def rotated_calls():
+    c0, ex = recording.load_npz(os.path.join(GOLDEN, "recorded_bos_rotated.npz"))
+    import copy
+    c1 = copy.copy(c0)
+    c1.simulate_density_gradients = bool(ex["call1_simulate_density_gradients"])
+    c1.ray_tracing_algorithm = int(ex["call1_ray_tracing_algorithm"])
+    assert str(ex["call1_density_grad_basename"]) == "sample-density.nrrd"
+    c1.density_grad_filename = os.path.join(GOLDEN, "sample-density.nrrd")
+    return (c0, c1), ex
+
+
+def test_rotated_recording_is_what_the_parameter_file_says():
+    (c0, c1), ex = rotated_calls()
+    assert (c0.num_particles, c0.lightray_number_per_particle) == (7225, 100)
+    assert c1.ray_tracing_algorithm == 1 and c0.elements[0].element_type == b"t"
+    assert c0.image_shape == (512, 512)
+    R = np.array(list(c0.camera.rotation_matrix)).reshape(3, 3)
+    assert abs(R[0, 0] - np.cos(np.deg2rad(150.0))) < 1e-6 and abs(abs(R[0, 2]) - 0.5) < 1e-6     # not the identity
+    Ri = np.array(list(c0.camera.inverse_rotation_matrix)).reshape(3, 3)
+    assert np.allclose(R @ Ri, np.eye(3), atol=1e-6)
+    # the field moves the rays: the two reference images differ
+    assert rel_l2(ex["ref_image1"], ex["ref_image0"]) > 1e-2
+
+
+def _rotated_dumps(lib, call, tmp_path):
+    call.source_point_number = call.num_particles
+    img, pos, dr = util.run_with_dumps(lib, call, str(tmp_path))
+    return img, pos, dr
+
+
+@pytest.mark.parametrize("which", ["oracle", "hostcheck"])
+def test_cpu_rotated_bos_matches_reference(which, oracle_lib, hostcheck_lib, tmp_path):
+    """CPU: the restatement and the product's stage code compiled for the host, on the rotated-camera call through
+    sample-density.nrrd, bit for bit on the rays the reference dumped."""
+    (_, c1), ex = rotated_calls()
+    img, pos, dr = _rotated_dumps(oracle_lib if which == "oracle" else hostcheck_lib, c1, tmp_path)
+    idx = ex["ray_index"]
+    assert len(pos) == 722500 and int(np.isfinite(pos[:, 0]).sum()) == int(ex["ref_hits"])
+    assert np.array_equal(pos[idx], ex["ref_pos"], equal_nan=True)
+    assert np.array_equal(dr[idx], ex["ref_dir"], equal_nan=True)
+    assert rel_l2(img, ex["ref_image1"]) <= 5e-6
+
+
+@pytest.mark.gpu
+def test_cuda_rotated_bos_matches_reference(cuda_lib, tmp_path):
+    """GPU: both calls of the rotated sample; the second marches through sample-density.nrrd with a non-identity
+    camera <-> volume rotation.  North-star tolerances on the reference's own ray dumps and images."""
+    (c0, c1), ex = rotated_calls()
+    img0 = c0.run(cuda_lib)
+    assert rel_l2(img0, ex["ref_image0"]) <= util.TOL_IMG_L2
+    plain = c1.run(cuda_lib)                                            # the non-dump kernel
+    assert rel_l2(plain, ex["ref_image1"]) <= util.TOL_IMG_L2
+    img, pos, dr = _rotated_dumps(cuda_lib, c1, tmp_path)
+    idx = ex["ray_index"]
+    m = util.compare((ex["ref_image1"], ex["ref_pos"], ex["ref_dir"]), (img, pos[idx], dr[idx]), 10.0)
+    print("rotated sample BOS vs reference:", m)
+    util.assert_parity("bos_rotated_euler", m)
+    assert abs(int(np.isfinite(pos[:, 0]).sum()) - int(ex["ref_hits"])) <= 2

@@ -11,7 +11,13 @@ The scripts are copied, never edited.  What the stage adds:
     and pins np.random.seed(None) so that recordings are reproducible;
   * LD_LIBRARY_PATH (pr03.py:1885 reads it).
 
-usage: python tools/stage_reference.py {piv|bos} --out DIR [--forward LIB] [--reference /root/reference]
+usage: python tools/stage_reference.py {piv|bos|bos_rotated} --out DIR [--forward LIB] [--reference /root/reference]
+
+kind bos_rotated = sample-data/bos/sample-parameters.mat (camera turned 150 degrees about y, Euler,
+thin lens, 512 x 512, one point per dot on a regular grid) -- the shipped parameter file whose rays DO cross
+sample-density.nrrd.  Its two absolute /scratch paths are re-pointed into the stage (density file, image
+directory) and the empty camera_design.pixel_gain is filled from bos_pattern.pixel_gain; every other field is
+written back as loaded.
 Needs /root/reference, so it runs in the build container; the recordings it writes are what
 travels (tests/golden/recorded_*.npz, see photon_b200/recording.py).
 """
@@ -47,6 +53,28 @@ np.random.seed = _pinned_seed
 '''
 
 
+def rotated_parameter_file(bos_dir):
+    """sample-data/bos/sample-parameters.mat with its two /scratch paths re-pointed into the stage."""
+    import numpy as np
+    import scipy.io as sio
+
+    def plain(v):
+        if hasattr(v, "_fieldnames"):
+            return {k: plain(getattr(v, k)) for k in v._fieldnames}
+        return v
+    m = sio.loadmat(os.path.join(bos_dir, "sample-parameters.mat"), squeeze_me=True, struct_as_record=False)
+    m = {k: plain(v) for k, v in m.items() if not k.startswith("__")}
+    m["density_gradients"]["density_gradient_filename"] = "../sample-data/bos/sample-density.nrrd"
+    m["output_data"]["image_directory"] = "../sample-data/bos/images_rotated/"
+    # camera_design.pixel_gain is an EMPTY array in the shipped file (pr03.py:1859 cannot convert it); the file keeps the
+    # gain under bos_pattern (25 dB, the value of the other sample file).  It only scales the 16-bit export.
+    if np.size(m["camera_design"]["pixel_gain"]) == 0:
+        m["camera_design"]["pixel_gain"] = float(m["bos_pattern"]["pixel_gain"])
+    os.makedirs(os.path.join(bos_dir, "parameters_rotated"), exist_ok=True)
+    os.makedirs(os.path.join(bos_dir, "images_rotated"), exist_ok=True)
+    sio.savemat(os.path.join(bos_dir, "parameters_rotated", "sample-parameters.mat"), m, format="5", long_field_names=True)
+
+
 def stage(kind, out, forward, reference):
     st = os.path.join(out, "stage")
     if os.path.exists(st):
@@ -70,7 +98,11 @@ def stage(kind, out, forward, reference):
     if os.path.exists(env["PHOTON_RECORD_DIR"]):
         shutil.rmtree(env["PHOTON_RECORD_DIR"])
     # sample_run_script.sh <kind>  ==  python3 batch_run_simulation.py ../sample-data/<kind>/parameters 1 1
-    cmd = [sys.executable, "batch_run_simulation.py", "../sample-data/%s/parameters" % kind, "1", "1"]
+    pdir = "../sample-data/%s/parameters" % kind
+    if kind == "bos_rotated":
+        pdir = "../sample-data/bos/parameters_rotated"
+        rotated_parameter_file(os.path.join(st, "sample-data", "bos"))
+    cmd = [sys.executable, "batch_run_simulation.py", pdir, "1", "1"]
     r = subprocess.run(cmd, cwd=os.path.join(st, "python_codes"), env=env, capture_output=True, text=True)
     with open(os.path.join(out, "run_%s.log" % kind), "w") as f:
         f.write(r.stdout + "\n--- stderr ---\n" + r.stderr)
@@ -79,7 +111,7 @@ def stage(kind, out, forward, reference):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("kind", choices=["piv", "bos"])
+    ap.add_argument("kind", choices=["piv", "bos", "bos_rotated"])
     ap.add_argument("--out", required=True)
     ap.add_argument("--forward", default="")
     ap.add_argument("--reference", default="/root/reference")
