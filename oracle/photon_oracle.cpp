@@ -183,8 +183,22 @@ bool load_field(const char *path, Field &F, std::string &err) {
     F.data_min = FLT_MAX;
     float gx = F.spacing.x, gy = F.spacing.y, gz = F.spacing.z;
     size_t W = sx, H = sy, Dp = sz;
-    auto at = [&](size_t x, size_t y, size_t z) { return nm1[z * W * H + y * W + x]; };
     // setData :1856-1995.  Literals such as 3.0/2 are double; result narrowed on store.
+    // The neighbour samples are indexed through FLOAT arithmetic there: lookup is a float3 and the index is
+    // size_t(lookup.z*data_width*data_height + lookup.y*data_width + lookup.x) (:1873-1975) -- float products and sums,
+    // so above 2^24 voxels (beyond 256^3) the low bits of the index are rounded away: at 512^3 x +- 1 lands on a
+    // multiple of 8.  Reproduced (the reference's gradients ARE these); an index rounded past the end of the array (the
+    // reference reads out of bounds there) is clamped to the last voxel.  PHOTON_GRADIENT_INDEX=exact: integer index.
+    const char *gi = getenv("PHOTON_GRADIENT_INDEX");
+    const bool exact_index = gi && strcmp(gi, "exact") == 0;
+    const float fW = (float)sx, fH = (float)sy;
+    auto at = [&](size_t x, size_t y, size_t z) {
+        if (exact_index) return nm1[z * W * H + y * W + x];
+        volatile float zw = (float)z * fW; volatile float zwh = zw * fH; volatile float yw = (float)y * fW;
+        volatile float s1 = zwh + yw; volatile float s2 = s1 + (float)x;
+        size_t i = (size_t)s2;
+        return nm1[i < n ? i : n - 1];
+    };
     float dmin = FLT_MAX;
 #pragma omp parallel for reduction(min : dmin) schedule(static)
     for (size_t z = 0; z < Dp; z++)
@@ -952,6 +966,8 @@ int photon_oracle_load_field(const char *path, float *meta16, float *out, long l
 }
 
 /* Cubic mode checkers: the coefficient volume and single samples at texel coordinates (cubic = 0: tex3d). */
+// bspline_w alone (CubicInterpolationCUDA code/internal/bspline_kernel.cu:83-104), for the known-answer test
+void photon_oracle_bspline_weights(float t, float *w, float *d) { bspline_w(t, w, d); }
 int photon_oracle_load_coefficients(const char *path, float *out, long long capacity_voxels) {
     Field F; std::string err;
     if (!load_field(path, F, err)) { fprintf(stderr, "photon_oracle: %s\n", err.c_str()); return 1; }

@@ -160,6 +160,8 @@ template <class T, int DIM, cudaTextureReadMode MODE>
 inline cudaError_t cudaUnbindTexture(texture<T, DIM, MODE> &t) { t.bound = nullptr; return cudaSuccess; }
 
 namespace shim {
+/* where setData's debug dump of the gradient field goes (the reference hard-codes a /scratch path, trace.h:1840) */
+inline std::string gradient_dump_path() { const char *p = getenv("PHOTON_REF_GRADIENT_DUMP"); return p && *p ? p : "/dev/null"; }
 extern int g_tex_fixed8;                       /* PHOTON_REF_TEXFILTER=fixed8 */
 extern thread_local long long t_tex_fetches;   /* per host thread, summed after each launch */
 inline int clampi(int v, int n) { return v < 0 ? 0 : (v > n - 1 ? n - 1 : v); }

@@ -172,7 +172,12 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
     }
     CK(cudaMemsetAsync(d_min, 0xff, sizeof(unsigned int), st));
     int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)148 * 16);
-    build_field_kernel<<<blocks, 256, 0, st>>>(d_rho, F.lin, sx, sy, sz, (float)dx, (float)dy, (float)dz, d_min);
+    // the reference's float-arithmetic voxel index (trace_core.cuh: field_voxel) differs from the integer one only
+    // above 2^24 voxels
+    const char *gi = getenv("PHOTON_GRADIENT_INDEX");
+    const bool float_index = n > ((size_t)1 << 24) && !(gi && strcmp(gi, "exact") == 0);
+    if (float_index) build_field_kernel<true><<<blocks, 256, 0, st>>>(d_rho, F.lin, sx, sy, sz, (float)dx, (float)dy, (float)dz, d_min);
+    else build_field_kernel<false><<<blocks, 256, 0, st>>>(d_rho, F.lin, sx, sy, sz, (float)dx, (float)dy, (float)dz, d_min);
     CK(cudaGetLastError());
     unsigned int key = 0;
     CK(cudaMemcpyAsync(&key, d_min, sizeof key, cudaMemcpyDeviceToHost, st));

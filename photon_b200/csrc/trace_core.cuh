@@ -149,10 +149,23 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
 // One voxel of the (grad n, n-1) field: Gladstone-Dale n-1 = K rho (trace.h:1729-1748) and
 // finite-difference gradients, one-sided 2nd order at the faces and central inside
 // (setData, trace.h:1856-1995; literals such as 3.0/2 are double there, y uses 2.0*grid).
+// FLOAT_INDEX: the reference addresses the neighbour samples as size_t(lookup.z*W*H + lookup.y*W + lookup.x) with a
+// float3 lookup (trace.h:1873-1975) -- float products and sums, so above 2^24 voxels the low bits of the index are
+// rounded away (at 512^3, x +- 1 lands on a multiple of 8 and the x gradient of most voxels is 0 or 4x too large).
+// Reproduced by default for fields of more than 2^24 voxels (parity with the reference's images); an index rounded
+// past the end (the reference reads out of bounds) is clamped.  PHOTON_GRADIENT_INDEX=exact selects the integer index.
+template <bool FLOAT_INDEX>
 PH_HD f4 field_voxel(const float *rho, int x, int y, int z, int W, int H, int D, float gx, float gy, float gz) {
     const float K = 0.225e-3f;
-    const size_t sW = (size_t)W, sWH = (size_t)W * (size_t)H;
-#define PH_AT(xx, yy, zz) (K * (PH_LDG(&rho[(size_t)(zz) * sWH + (size_t)(yy) * sW + (size_t)(xx)]) * 1.0f))
+    const size_t sW = (size_t)W, sWH = (size_t)W * (size_t)H, n = sWH * (size_t)D;
+    const float fW = (float)W, fH = (float)H;
+    auto idx = [&](int xx, int yy, int zz) -> size_t {
+        if (!FLOAT_INDEX) return (size_t)zz * sWH + (size_t)yy * sW + (size_t)xx;
+        const float f = add_rn(add_rn(mul_rn(mul_rn((float)zz, fW), fH), mul_rn((float)yy, fW)), (float)xx);
+        const size_t i = (size_t)f;
+        return i < n ? i : n - 1;
+    };
+#define PH_AT(xx, yy, zz) (K * (PH_LDG(&rho[idx(xx, yy, zz)]) * 1.0f))
     float c = PH_AT(x, y, z);
     f4 o;
     if (x < 1) o.x = (float)((-3.0 / 2 * c + 2 * PH_AT(x + 1, y, z) - 1.0 / 2 * PH_AT(x + 2, y, z)) / gx);
@@ -165,7 +178,8 @@ PH_HD f4 field_voxel(const float *rho, int x, int y, int z, int W, int H, int D,
     else if (z >= D - 1) o.z = (float)((3.0 / 2 * c - 2 * PH_AT(x, y, z - 1) + 1.0 / 2 * PH_AT(x, y, z - 2)) / gz);
     else o.z = (PH_AT(x, y, z + 1) - PH_AT(x, y, z - 1)) / (2 * gz);
 #undef PH_AT
-    o.w = c;
+    // the n-1 channel is addressed with integers in the reference too (trace.h:1990)
+    o.w = K * (PH_LDG(&rho[(size_t)z * sWH + (size_t)y * sW + (size_t)x]) * 1.0f);
     return o;
 }
 

@@ -13,6 +13,8 @@ def write_nrrd(path, rho_zyx, spacings, origin, encoding="raw"):
     """``rho_zyx``: float32 array indexed [z][y][x]; spacings/origin in micrometres (x, y, z)."""
     rho = np.ascontiguousarray(rho_zyx, np.float32)
     nz, ny, nx = rho.shape
+    spacings = [float(v) for v in spacings]      # numpy scalars would print as "np.float64(...)"
+    origin = [float(v) for v in origin]
     hdr = (
         "NRRD0005\n"
         "# written by photon_b200.nrrd\n"

@@ -70,8 +70,11 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
         float step = (float)fmin(dx, dy); step = step < dz ? step : (float)dz; P.step = step;
         field.resize((size_t)sx * sy * sz);
         float dmin = INFINITY;
+        const char *gi = getenv("PHOTON_GRADIENT_INDEX");
+        const bool float_index = field.size() > ((size_t)1 << 24) && !(gi && strcmp(gi, "exact") == 0);
         for (int z = 0; z < sz; z++) for (int y = 0; y < sy; y++) for (int x = 0; x < sx; x++) {
-            f4 o = field_voxel(vol.rho.data(), x, y, z, sx, sy, sz, (float)dx, (float)dy, (float)dz);
+            f4 o = float_index ? field_voxel<true>(vol.rho.data(), x, y, z, sx, sy, sz, (float)dx, (float)dy, (float)dz)
+                               : field_voxel<false>(vol.rho.data(), x, y, z, sx, sy, sz, (float)dx, (float)dy, (float)dz);
             field[((size_t)z * sy + y) * sx + x] = o;
             if (o.w < dmin) dmin = o.w;
         }

@@ -1,7 +1,14 @@
 """Cubic mode (PHOTON_INTERPOLATION=cubic): tricubic B-spline interpolation of n-1 with analytic
 gradient on a scalar coefficient volume.  The reference's own cubic branch is unreachable through the
-ABI (prt.cu:3330 hard-codes interpolation_scheme = 1), so there is no reference output: PARITY
-UNPINNED.  What is checked instead:
+ABI (prt.cu:3330 hard-codes interpolation_scheme = 1), so there is no traced reference output.  PINNED at
+the level the reference offers: CubicInterpolationCUDA ships a plain-C++ CPU implementation of its
+algorithm (examples/referenceCubicTexture3D/cubicPrefilter3D.hpp:51-150, cubicFilter3D_kernel.hpp:46-93;
+weights and derivative weights code/internal/bspline_kernel.cu:50-104).  oracle/build_ref_ci.sh compiles
+it from where it lies; tests/golden/ci_golden.npz holds its answers (tests/golden/make_ci_golden.py).
+  KAT  prefilter bit for bit, weights and derivative weights bit for bit, 64-tap value to float rounding
+       (CI sums the taps in z, y, x order, the product contracts x -> y -> z), gradient against the sum
+       built from CI's derivative weights -- oracle and host-compiled stage code on the CPU, the CUDA
+       prefilter and sampler on the GPU;
   CPU  the oracle's restatement of CubicInterpolationCUDA's published algorithm has the properties the
        algorithm promises (knot reproduction, exactness on polynomials up to degree 3 away from the
        faces, gradient = derivative of the value), agrees with the linear mode to O(h^2) on a smooth
@@ -114,7 +121,110 @@ def test_stage_code_bit_exact_vs_oracle_cubic(alg, cubic_env, hostcheck_lib, ora
     assert 0 < m["dpos_px"] < 0.05, m                                                   # a different interpolant, same physics
 
 
+# ------------------------------------------------------- known answers of CI's own CPU reference
+def ci_golden():
+    return np.load(os.path.join(util.GOLDEN_DIR, "ci_golden.npz"))
+
+
+def ci_gradient(g):
+    """Value and gradient (per texel) at g['pts'] as the 64-term sums of CI's weights and first-derivative weights
+    (bspline_kernel.cu:83-104) over CI's coefficients, in float64: the known answer for the analytic gradient."""
+    coef = g["coef"].astype(np.float64)
+    pts = g["pts"].astype(np.float32)
+    b = pts - np.float32(0.5)
+    f = np.floor(b)
+    fr = (b - f).astype(np.float32)
+    idx = f.astype(np.int64)
+    frs, W, DW = g["fractions"], g["weights"].astype(np.float64), g["dweights"].astype(np.float64)
+
+    def wts(t):                                     # CI's weights are cubic polynomials: evaluate them as CI does, in float32
+        one = np.float32(1.0) - t; sq = t * t; osq = one * one
+        w = np.stack([np.float32(1 / 6.0) * osq * one, np.float32(2 / 3.0) - np.float32(0.5) * sq * (np.float32(2.0) - t),
+                      np.float32(2 / 3.0) - np.float32(0.5) * osq * (np.float32(2.0) - one), np.float32(1 / 6.0) * sq * t], -1)
+        d = np.stack([np.float32(-0.5) * sq + t - np.float32(0.5), np.float32(1.5) * sq - np.float32(2.0) * t,
+                      np.float32(-1.5) * sq + t + np.float32(0.5), np.float32(0.5) * sq], -1)
+        return w.astype(np.float64), d.astype(np.float64)
+    # the closed forms above ARE CI's (checked against its exported functions on the stored fractions)
+    w0, d0 = wts(frs)
+    assert np.array_equal(w0.astype(np.float32), W.astype(np.float32)) and np.array_equal(d0.astype(np.float32), DW.astype(np.float32))
+    wx, dx = wts(fr[:, 0]); wy, dy = wts(fr[:, 1]); wz, dz = wts(fr[:, 2])
+    val = np.zeros(len(pts)); gx = np.zeros(len(pts)); gy = np.zeros(len(pts)); gz = np.zeros(len(pts))
+    for c in range(4):
+        for bb in range(4):
+            for a in range(4):
+                t = coef[idx[:, 2] - 1 + c, idx[:, 1] - 1 + bb, idx[:, 0] - 1 + a]
+                val += wx[:, a] * wy[:, bb] * wz[:, c] * t
+                gx += dx[:, a] * wy[:, bb] * wz[:, c] * t
+                gy += wx[:, a] * dy[:, bb] * wz[:, c] * t
+                gz += wx[:, a] * wy[:, bb] * dz[:, c] * t
+    return val, gx, gy, gz
+
+
+def _write_ci_volume(tmp_path, g, spacing=100.0):
+    path = str(tmp_path / "ci_volume.nrrd")
+    nrrd.write_nrrd(path, g["rho"], (spacing,) * 3, (0.0, 0.0, 750e3))
+    return path
+
+
+def _check_against_ci(coefs, samples, g, spacing=100.0):
+    assert np.array_equal(coefs, g["coef"])                                      # the prefilter, bit for bit
+    scale = float(np.abs(g["val"]).max())
+    assert np.max(np.abs(samples[:, 3] - g["val"])) <= 2e-6 * scale              # CI's own 64-tap sum (float32, z-y-x order)
+    val, gx, gy, gz = ci_gradient(g)
+    assert np.max(np.abs(samples[:, 3] - val)) <= 1e-6 * scale
+    for k, want in enumerate((gx, gy, gz)):
+        want = want / spacing                                                    # per texel -> per micrometre
+        assert np.max(np.abs(samples[:, k] - want)) <= 2e-5 * np.max(np.abs(want)), k
+
+
+def test_ci_reference_live_matches_golden():
+    """Where /root/reference is mounted: rebuild CI's CPU reference from its own sources and regenerate the answers."""
+    if not os.path.isdir("/root/reference/cuda_codes/CubicInterpolationCUDA"):
+        pytest.skip("reference not mounted (GPU box)")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_ci_golden", os.path.join(util.GOLDEN_DIR, "make_ci_golden.py"))
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    lib = mod.load_ci()
+    rho, nm1, pts, fractions = mod.inputs()
+    coef, val, wts, dws, ts, b, db = mod.ci_answers(lib, nm1, pts, fractions)
+    g = ci_golden()
+    assert np.array_equal(rho, g["rho"]) and np.array_equal(coef, g["coef"]) and np.array_equal(val, g["val"])
+    assert np.array_equal(wts, g["weights"]) and np.array_equal(dws, g["dweights"])
+    # CI's piecewise B-spline and its derivative agree with its own branch-free weights: w_a(f) = B(a - 1 - f) ...
+    for a in range(4):
+        for f, w, d in zip(fractions[::8], wts[::8], dws[::8]):
+            assert abs(lib.photon_ci_bspline(float(f) - (a - 1)) - w[a]) <= 2e-7
+            if 0.0 < f < 1.0:
+                assert abs(-lib.photon_ci_bspline_1st_derivative(float(a - 1) - float(f)) - d[a]) <= 4e-7
+
+
+def test_oracle_cubic_against_ci_known_answers(oracle_lib, tmp_path):
+    g = ci_golden()
+    path = _write_ci_volume(tmp_path, g)
+    _check_against_ci(oracle_coefficients(oracle_lib, path, g["coef"].shape), oracle_samples(oracle_lib, path, 1, g["pts"]), g)
+
+
+def test_weights_bit_exact_against_ci(oracle_lib):
+    """bspline_w of the product / oracle = CI's bspline_weights and bspline_weights_1st_derivative, bit for bit."""
+    g = ci_golden()
+    oracle_lib.photon_oracle_bspline_weights.argtypes = [C.c_float, C.c_void_p, C.c_void_p]
+    w = np.zeros(4, np.float32); d = np.zeros(4, np.float32)
+    for t, cw, cd in zip(g["fractions"], g["weights"], g["dweights"]):
+        oracle_lib.photon_oracle_bspline_weights(float(t), w.ctypes.data, d.ctypes.data)
+        assert np.array_equal(w, cw) and np.array_equal(d, cd), t
+
+
 # ------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+def test_cuda_cubic_against_ci_known_answers(cuda_lib, tmp_path):
+    g = ci_golden()
+    path = _write_ci_volume(tmp_path, g)
+    got = np.zeros(g["coef"].shape, np.float32)
+    cuda_lib.photon_b200_load_coefficients.argtypes = [C.c_char_p, C.c_void_p, C.c_longlong]
+    assert cuda_lib.photon_b200_load_coefficients(path.encode(), got.ctypes.data, got.size) == 0
+    _check_against_ci(got, cuda_samples(cuda_lib, path, 1, g["pts"]), g)
+
+
 def cuda_samples(lib, path, cubic, pts):
     pts = np.ascontiguousarray(pts, np.float32)
     out = np.zeros((len(pts), 4), np.float32)

@@ -66,20 +66,24 @@ def test_texture_mode_matches_reference_cuda(name, cases, reference_cuda, cuda_l
 
 @pytest.mark.parametrize("name", CASE_NAMES)
 def test_default_mode_matches_reference_cuda(name, cases, reference_cuda, cuda_lib, tmp_path):
-    """The product's default sampler (exact float weights; the hot loops the benchmark times) against the reference's
-    CUDA path with its 8-bit hardware filter weights.  Scenes without a field: strict.  Scenes with a field: the
-    difference IS the hardware's weight quantisation (DESIGN 5 states the measured distances)."""
+    """The product's DEFAULT sampler (exact float weights; the hot loops the benchmark times) against the reference's
+    CUDA path with its 8-bit hardware filter weights.  North-star bounds on every scene but the two adaptive /
+    multistep integrators, whose literal use of n-1 where n is meant (trace.h:425, 430, 683, 1293-1453) amplifies the
+    weight quantisation: measured on B200 (profiles/README.md, r4a) rk45 1.5e-3 px max / 7.8e-4 at the 99.9th
+    percentile, adams-bashforth 2.5 px max / 0.81 px at the 99th -- with the SAME sampler (texture mode, above) both
+    are bit-exact, so that distance is the sampler's, not the integrators'."""
     call, pitch = cases[name]
     got = util.run_with_dumps(cuda_lib, call, str(tmp_path))
     m = util.compare(reference_cuda(name), got, pitch)
     print("default mode vs reference CUDA:", name, cuda_lib.photon_b200_last_variant().decode(), m)
-    if name not in FIELD:
-        _strict(name, m)
+    if name == "bos_rk45_thin_diffraction":
+        assert m["nan_mismatch"] == 0 and m["ddir_rad"] <= util.TOL_DIR_RAD, m
+        assert m["dpos_px_p999"] <= util.TOL_POS_PX and m["dpos_px"] <= 4e-3 and m["image_rel_l2"] <= util.TOL_IMG_L2, m
+    elif name in util.AB4_CASES:
+        assert m["nan_mismatch"] == 0 and m["ddir_rad"] <= util.TOL_DIR_RAD, m
+        assert m["dpos_px_p99"] <= 1.5 and m["dpos_px"] <= 2 * util.AB4_MAX_PX, m
     else:
-        assert m["nan_mismatch"] <= max(2, m["rays"] // 5000), m
-        assert m["ddir_rad"] <= util.TOL_DIR_RAD, (name, m)
-        bound = util.AB4_MAX_PX if name in util.AB4_CASES else 5e-3
-        assert m["dpos_px_p99"] <= bound and m["dpos_px"] <= (util.AB4_MAX_PX if name in util.AB4_CASES else 2e-2), (name, m)
+        _strict(name, m)
 
 
 @pytest.mark.parametrize("name", ["bos_rk4_thin_diffraction", "bos_euler_thin_diffraction"])
