@@ -27,6 +27,11 @@
  *   PHOTON_TIMING=1         per-stage wall times of start_ray_tracing on stderr
  *   PHOTON_INTERPOLATION=cubic  tricubic B-spline sampler on a prefiltered scalar volume (default: linear)
  *   PHOTON_MORTON=<0|1>     CTAs take the source points in Morton order of (x, y) [default 1 with a density field]
+ *   PHOTON_RAY_ORDER=<0|1>  the rays of a source point are walked in Morton order of their aim points on the lens, so a
+ *                           warp's lanes cross the field side by side [default 1 with a density field]; ray ids, dumps,
+ *                           noise streams and dot statistics keep the caller's order
+ *   PHOTON_GRADIENT_INDEX=exact  integer voxel index in the gradient stencil instead of the reference's float-arithmetic
+ *                           index (which loses its low bits above 2^24 voxels, trace.h:1873-1975) [default: reference]
  *   PHOTON_HOT=<4|5>        RK4 hot loop: 5 = z-neighbour short path (coherent rays), 4 = without; default by the
  *                           width of a source point's cone against the grid spacing
  *   PHOTON_NCCL=0           PHOTON_GPUS: sum the partial images through the host instead of one ncclReduce

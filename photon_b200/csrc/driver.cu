@@ -15,6 +15,7 @@
 #include <sys/stat.h>
 #include <chrono>
 #include <limits>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -106,8 +107,35 @@ bool find_mem_field(const char *path, MemField &out) {
     return false;
 }
 
+// The NRRD file is read ONCE per (path, mtime, size) however many devices build a field from it at the same time (the
+// device threads of a PHOTON_GPUS call all arrive here together; eight reads + eight 512 MB vectors cost the cold call
+// of round 1 seconds).  The first thread reads, the others wait on the entry's mutex and share the host copy; the copy
+// lives as long as somebody holds it (weak cache).
+struct SharedVolume { std::mutex mu; bool loaded = false, ok = false; pnrrd::Volume vol; };
+std::mutex g_vol_mutex;
+std::vector<std::pair<std::string, std::weak_ptr<SharedVolume>>> g_volumes;
+std::shared_ptr<SharedVolume> shared_volume(const char *path) {
+    struct stat sb;
+    std::string key = path;
+    if (stat(path, &sb) == 0) key += "|" + std::to_string((long long)sb.st_mtim.tv_sec) + "." + std::to_string((long long)sb.st_mtim.tv_nsec) + "|" + std::to_string((long long)sb.st_size);
+    std::shared_ptr<SharedVolume> v;
+    {
+        std::lock_guard<std::mutex> lk(g_vol_mutex);
+        for (size_t i = 0; i < g_volumes.size();) {
+            if (g_volumes[i].second.expired()) { g_volumes.erase(g_volumes.begin() + i); continue; }
+            if (g_volumes[i].first == key) v = g_volumes[i].second.lock();
+            i++;
+        }
+        if (!v) { v = std::make_shared<SharedVolume>(); g_volumes.emplace_back(key, v); }
+    }
+    std::lock_guard<std::mutex> lk(v->mu);
+    if (!v->loaded) { v->ok = pnrrd::load(path, v->vol); v->loaded = true; }
+    return v;
+}
+
 bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) {
-    pnrrd::Volume vol;
+    pnrrd::Volume vol;                   // header fields only (the voxels stay in the shared copy)
+    std::shared_ptr<SharedVolume> shared;
     MemField mem{};
     const bool from_memory = strncmp(path, "mem:", 4) == 0;
     const float *src = nullptr;
@@ -121,12 +149,15 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
         for (int i = 0; i < 3; i++) { vol.spacing[i] = mem.spacing[i]; vol.origin[i] = mem.origin[i]; }
         src = mem.rho;
     } else {
-        if (!pnrrd::load(path, vol)) {
-            g_error = std::string("failed to load \"") + path + "\": " + vol.error;
+        shared = shared_volume(path);
+        if (!shared->ok) {
+            g_error = std::string("failed to load \"") + path + "\": " + shared->vol.error;
             fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
             return false;
         }
-        src = vol.rho.data();
+        vol.nx = shared->vol.nx; vol.ny = shared->vol.ny; vol.nz = shared->vol.nz;
+        for (int i = 0; i < 3; i++) { vol.spacing[i] = shared->vol.spacing[i]; vol.origin[i] = shared->vol.origin[i]; }
+        src = shared->vol.rho.data();
     }
     int sx = vol.nx, sy = vol.ny, sz = vol.nz;
     // bounds from the header (trace.h:1698-1706); NRRD z origin is shifted by -750e3
@@ -380,6 +411,7 @@ struct photon_scene {
     float *d_sx = nullptr, *d_sy = nullptr, *d_sz = nullptr; double *d_srad = nullptr; int *d_sdiam = nullptr;
     float *d_angle = nullptr, *d_irr = nullptr;
     f2 *d_aim = nullptr;
+    int *d_ray_order = nullptr;          // Morton order of the aim points within a source point, or null
     float *d_image = nullptr;
     unsigned long long *d_fixed = nullptr;   // deterministic mode (PHOTON_DETERMINISTIC=1)
     double fixed_scale = 0.0;
@@ -392,6 +424,7 @@ struct photon_scene {
     int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
     double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
     int *d_order = nullptr;              // processing order of the source points (Morton order of x, y), or null
+    bool grouped = false;                // fan-out rays: CTAs own groups of 32 neighbouring points, lanes = points (PHOTON_GROUP)
     bool coherent = false;               // rays of a source point stay within ~a cell of each other: v5 hot loop
     bool use_cells = false;              // ... and the field has its per-cell polynomial table (PHOTON_CELLS, default on)
     long long n_dots = 0, rays_per_dot = 0;
@@ -445,6 +478,10 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     a.inter_pos = ipos; a.inter_dir = idir; a.n_inter = n_inter;
     const bool dump = fpos != nullptr || ipos != nullptr;
     int grid = std::min(point_count, s->grid_blocks);
+    // fan-out scenes: a CTA owns 32 neighbouring source points and a warp's lanes trace one ray of each (trace_kernel.cuh)
+    const bool grouped = s->grouped && s->d_dots == nullptr && !s->d_fixed && !s->use_texture && !s->use_cubic &&
+                         a.simulate_gradients && (a.algorithm == 1 || a.algorithm == 2);
+    if (grouped) grid = std::min((point_count + 31) / 32, s->grid_blocks);
     a.dot_stats = s->d_dots; a.rays_per_dot = s->rays_per_dot; a.n_dots = s->n_dots;
     a.order = dump ? nullptr : s->d_order;
     const bool stats = s->d_dots != nullptr;
@@ -504,8 +541,10 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         int g = (stats || fixed || !a.simulate_gradients) ? G_FANOUT : s->use_cells ? G_CELLS : s->coherent ? G_COHERENT : G_FANOUT;
         if (g == G_CELLS && occ != 3) g = G_COHERENT;
         if (g == G_COHERENT && occ != 3 && occ != 5) g = G_FANOUT;
-        gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : "fanout";
-        if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : grouped ? "fanout32" : "fanout";
+        if (grouped && g == G_FANOUT && dump) trace_rays_kernel<true, 2, LinearField, false, PH_BLOCK, false, 1, 32><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (grouped && g == G_FANOUT) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, false, 1, 32><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        else if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump && g == G_CELLS) trace_rays_kernel<true, 2, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, SC);
@@ -681,9 +720,19 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
                          ne, element_center, element_data, element_plane_parameters, element_system_index, cam,
                          algorithm, add_pos_noise, pos_noise_std, add_ngrad_noise, ngrad_noise_std, cone_ratio, g_error))
         return false;
+    std::vector<int> ray_order;
     if (!a.philox) {
         if (!upload(s->d_aim, aim.data(), aim.size(), s->stream, s->pool)) return false;
-        CK(cudaStreamSynchronize(s->stream));    // aim is a local buffer
+        // rays of a source point in Morton order of their aim points (PHOTON_RAY_ORDER, default on with a density field
+        // and at least two warps of rays per point)
+        const char *ro = getenv("PHOTON_RAY_ORDER");
+        const bool want = ro ? atoi(ro) != 0 : (simulate_density_gradients && rpp >= 64);
+        if (want) {
+            morton_ray_order(aim, ray_order);
+            if (!upload(s->d_ray_order, ray_order.data(), ray_order.size(), s->stream, s->pool)) return false;
+            a.ray_order = s->d_ray_order;
+        }
+        CK(cudaStreamSynchronize(s->stream));    // aim and ray_order are local buffers
         a.aim = s->d_aim;
     }
     Camera &c = a.cam;
@@ -702,6 +751,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         // coherent rays: the cone of a source point at the lens (cone_ratio * lens_pitch) is narrower than a cell
         s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
         if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;
+        { const char *gp = getenv("PHOTON_GROUP"); s->grouped = !s->coherent && s->npoints >= 64 && !(gp && atoi(gp) == 0); }
         std::lock_guard<std::mutex> field_lock(s->field->mu);            // the on-demand tables below are added under it
         { const char *pc = getenv("PHOTON_CELLS");
           s->use_cells = s->coherent && algorithm == 2 && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }   // only rk4_hot reads it
@@ -797,7 +847,7 @@ void photon_scene_destroy(photon_scene *s) {
     cudaStream_t st = s->stream;
     pool_free(s->d_sx, st); pool_free(s->d_sy, st); pool_free(s->d_sz, st); pool_free(s->d_srad, st); pool_free(s->d_sdiam, st);
     pool_free(s->d_angle, st); pool_free(s->d_irr, st); pool_free(s->d_aim, st); pool_free(s->d_image, st); pool_free(s->d_counters, st);
-    pool_free(s->d_fixed, st); pool_free(s->d_dots, st); pool_free(s->d_order, st);
+    pool_free(s->d_fixed, st); pool_free(s->d_dots, st); pool_free(s->d_order, st); pool_free(s->d_ray_order, st);
     if (st) cudaStreamSynchronize(st);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -1189,8 +1239,10 @@ int nccl_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
     for (int g = 0; g < n; g++) { cudaSetDevice(res[g].scene->device); if (cudaStreamSynchronize(res[g].scene->stream) != cudaSuccess) { cudaGetLastError(); return 2; } }
     return 0;
 }
+void nccl_prepare(int n) { std::lock_guard<std::mutex> lk(g_nccl.mu); g_nccl.ensure(n); }
 #else
 int nccl_reduce_images(std::vector<ShardResult> &, int, size_t) { return 1; }
+void nccl_prepare(int) {}
 #endif
 
 }  // namespace
@@ -1296,6 +1348,8 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
     // GPU, private images, one sum at the end.  One host thread per device.
     std::vector<ShardResult> res((size_t)ngpus);
     std::vector<std::thread> th;
+    // communicator set-up (0.67 s on the first call of a process) runs beside the field builds, not after the trace
+    std::thread nccl_init([ngpus]() { nccl_prepare(ngpus); });
     for (int g = 0; g < ngpus; g++) {
         th.emplace_back([&, g]() {
             photon_scene *s = make_scene(shard_index * ngpus + g, shard_count * ngpus, g);
@@ -1306,6 +1360,7 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
         });
     }
     for (auto &t : th) t.join();
+    nccl_init.join();
     bool all_ok = true;
     for (int g = 0; g < ngpus; g++) if (!res[g].ok) { fprintf(stderr, "libparallel_ray_tracing(b200): GPU %d failed; image untouched\n", g); all_ok = false; }
     auto destroy_all = [&]() { for (int g = 0; g < ngpus; g++) if (res[g].scene) photon_scene_destroy(res[g].scene); };

@@ -3,8 +3,10 @@
 // draws, double -> float element arrays, the stage order of the optical train, camera.
 // Device pointers (sources, Mie table, aim table, field, image) are set by the caller.
 #pragma once
+#include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -13,6 +15,29 @@
 #include "trace_core.cuh"
 
 namespace ph {
+
+// Morton (Z-order) rank of the lens aim points of one source point: rays that are neighbours in the processing order
+// aim at neighbouring points of the aperture, so the 32 lanes of a warp march through neighbouring cells of the
+// density field and their cell loads fall on the same lines (north-star (b): "reordering rays by Morton key").
+// 16 bits per axis over the bounding box of the aim points; stable counting sort is overkill for <= 1e4 rays.
+inline void morton_ray_order(const std::vector<f2> &aim, std::vector<int> &order) {
+    const size_t n = aim.size();
+    order.resize(n);
+    if (n == 0) return;
+    float x0 = aim[0].x, x1 = x0, y0 = aim[0].y, y1 = y0;
+    for (auto &p : aim) { x0 = std::min(x0, p.x); x1 = std::max(x1, p.x); y0 = std::min(y0, p.y); y1 = std::max(y1, p.y); }
+    const float kx = x1 > x0 ? 65535.0f / (x1 - x0) : 0.0f, ky = y1 > y0 ? 65535.0f / (y1 - y0) : 0.0f;
+    auto spread = [](uint32_t v) { v &= 0xffffu; v = (v | (v << 8)) & 0x00ff00ffu; v = (v | (v << 4)) & 0x0f0f0f0fu;
+                                   v = (v | (v << 2)) & 0x33333333u; v = (v | (v << 1)) & 0x55555555u; return v; };
+    std::vector<std::pair<uint32_t, int>> key(n);
+    for (size_t i = 0; i < n; i++) {
+        const uint32_t qx = (uint32_t)std::min(65535.0f, std::max(0.0f, (aim[i].x - x0) * kx));
+        const uint32_t qy = (uint32_t)std::min(65535.0f, std::max(0.0f, (aim[i].y - y0) * ky));
+        key[i] = {spread(qx) | (spread(qy) << 1), (int)i};
+    }
+    std::stable_sort(key.begin(), key.end(), [](const std::pair<uint32_t, int> &a, const std::pair<uint32_t, int> &b) { return a.first < b.first; });
+    for (size_t i = 0; i < n; i++) order[i] = key[i].second;
+}
 
 inline bool fill_scene_args(TraceArgs &a, std::vector<f2> &aim, float lens_pitch, float image_distance,
                             const scattering_data_t *sc, const char *scattering_type_str,

@@ -35,6 +35,7 @@ struct TraceArgs {
     int global_point_offset;             // index of shard point 0 in the caller's arrays (RNG keys)
     // lens samples: table of aim points [rpp] (reference draws) or Philox per ray
     const f2 *aim;
+    const int *ray_order;                // slot k of a source point traces ray ray_order[k] (Morton order of the aim points), or null
     int philox;
     unsigned int seed;
     // noise (reference: cuRAND XORWOW seeded with time(); here Philox streams)

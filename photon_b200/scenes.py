@@ -226,11 +226,12 @@ def c1_piv(*, particles=50000, rays_per_particle=10000, nx=1024, ny=1024, seed=1
     return call
 
 
-def turbulent_field(n, *, seed=1, k_lo=4.0, k_hi=128.0, rms=0.05, rho0=1.225, device=None):
+def turbulent_field(n, *, seed=1, k_lo=4.0, k_hi=128.0, rms=0.05, rho0=1.225, device=None, keep_on_device=False):
     """Band-limited Gaussian random density field of BASELINE.md C4: white noise from
     ``default_rng(seed)`` shaped in Fourier space to E(k) ~ k^-5/3 for k_lo <= |k| <= k_hi (cycles
     per box), zero elsewhere, scaled to an rms of ``rms`` around ``rho0``.  float32 [z][y][x].
-    The FFT runs with numpy, or with torch on ``device`` (the 1024^3 case takes minutes on a CPU).
+    The FFT runs with numpy, or with torch on ``device`` (the 1024^3 case takes minutes on a CPU);
+    ``keep_on_device`` returns the torch tensor instead of copying the 4 GiB back to the host.
     Amplitude per mode = sqrt(E(k) / (4 pi k^2)) ~ k^(-11/6)."""
     rng = np.random.default_rng(seed)
     w = rng.standard_normal((n, n, n), dtype=np.float32)
@@ -251,7 +252,8 @@ def turbulent_field(n, *, seed=1, k_lo=4.0, k_hi=128.0, rms=0.05, rho0=1.225, de
         del F
         f *= rms / f.std()
         f += rho0
-        return f.to(torch.float32).cpu().numpy()
+        f = f.to(torch.float32).contiguous()
+        return f if keep_on_device else f.cpu().numpy()          # keep_on_device: hand it over with "mem:<name>"
     F = np.fft.rfftn(w)
     k = np.sqrt(kz[:, None, None] ** 2 + kz[None, :, None] ** 2 + kx[None, None, :] ** 2)
     amp = np.where((k >= k_lo) & (k <= k_hi), np.maximum(k, 1.0) ** (-11.0 / 6.0), 0.0)
@@ -261,7 +263,7 @@ def turbulent_field(n, *, seed=1, k_lo=4.0, k_hi=128.0, rms=0.05, rho0=1.225, de
 
 
 def c4_piv(nrrd_path, *, n=1024, particles=1000000, rays_per_particle=1000, nx=2048, ny=2048,
-           write_field=True, seed=2, device=None, frame_shift_um=0.0, source_point_number=10000):
+           write_field=True, seed=2, device=None, frame_shift_um=0.0, source_point_number=10000, lib=None):
     """PIV with Mie-scattering particles seen through a turbulent density field.
 
     n^3 band-limited random field (:func:`turbulent_field`, k = 4..min(128, n/4)), extent 200 mm,
@@ -282,7 +284,16 @@ def c4_piv(nrrd_path, *, n=1024, particles=1000000, rays_per_particle=1000, nx=2
     call.diameter_index = np.random.default_rng(seed + 1).integers(0, 27, particles).astype(np.int32)
     extent = 200e3
     spacing = extent / (n - 1)
-    if write_field:
+    if write_field and str(nrrd_path).startswith("mem:"):
+        # the field is made on the GPU and handed over in memory (no 4 GiB round trip through a file); the call keeps it alive
+        from .nrrd import register_field
+        rho = turbulent_field(n, seed=1, k_hi=min(128.0, n / 4.0), device=device, keep_on_device=device is not None)
+        if device is not None:
+            call._field_keepalive = rho
+            register_field(lib, str(nrrd_path)[4:], (rho.data_ptr(), tuple(rho.shape)), (spacing,) * 3, (-extent / 2, -extent / 2, 450e3))
+        else:
+            call._field_keepalive = register_field(lib, str(nrrd_path)[4:], rho, (spacing,) * 3, (-extent / 2, -extent / 2, 450e3))
+    elif write_field:
         rho = turbulent_field(n, seed=1, k_hi=min(128.0, n / 4.0), device=device)
         write_nrrd(nrrd_path, rho, (spacing,) * 3, (-extent / 2, -extent / 2, 450e3))
     call.source_point_number = source_point_number

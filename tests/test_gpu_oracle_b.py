@@ -106,9 +106,11 @@ def test_host_fixed8_filter_model_against_hardware(name, cases, reference_cuda, 
 
 def test_texture_unit_weights_are_8_bit(cuda_lib, tmp_path):
     """The unit itself, one sample at a time (photon_b200_sample_field, mode 2 = tex3D<float4> on the field's texture
-    object): against numpy trilinear blends with exact fractions and with fractions rounded to 1/256."""
+    object) on WHITE-NOISE texels, where every bit of a weight shows.  Measured on B200 (tools/texprobe.py, profiles
+    r4c): along ONE axis the weight is exactly round(frac * 256) / 256; with two or three fractional axes the result sits
+    within ~4e-3 of full scale of the blend with those weights (mean 3e-4) -- closer than the exact-fraction blend, but
+    not explained by any per-axis rounding rule: the unit's weight products carry limited precision of their own."""
     import ctypes as C
-    from photon_b200 import scenes
     from photon_b200.nrrd import write_nrrd
     n = 24
     rng = np.random.default_rng(5)
@@ -118,26 +120,29 @@ def test_texture_unit_weights_are_8_bit(cuda_lib, tmp_path):
     meta = np.zeros(16, np.float32)
     texels = np.zeros((n, n, n, 4), np.float32)
     assert cuda_lib.photon_b200_load_field(path.encode(), meta.ctypes.data, texels.ctypes.data, n ** 3) == 0
-    pts = (1.0 + rng.random((4096, 3)) * (n - 3)).astype(np.float32)
+    pts = (1.0 + rng.random((8192, 3)) * (n - 3)).astype(np.float32)
+    pts[:2048, 1:] = np.floor(pts[:2048, 1:]) + 0.5                      # y, z on texel centres: a 1-D probe of the x weight
+    pts[:2048, 0] = np.floor(pts[:2048, 0]) + 0.5 + np.arange(2048, dtype=np.float32) / 2048.0
     hw = np.zeros((len(pts), 4), np.float32)
     assert cuda_lib.photon_b200_sample_field(path.encode(), 2, len(pts), pts.ctypes.data, hw.ctypes.data) == 0
+    b = pts - np.float32(0.5)
+    f = np.floor(b)
+    fr = (b - f).astype(np.float64)
+    i = f.astype(np.int64)
 
-    def blend(quant):
-        b = pts.astype(np.float32) - np.float32(0.5)
-        f = np.floor(b)
-        fr = (b - f).astype(np.float32)
-        if quant:
-            fr = (np.floor(fr * np.float32(256.0) + np.float32(0.5)) / np.float32(256.0)).astype(np.float32)
-        i = f.astype(np.int64)
+    def blend(w):
         out = np.zeros((len(pts), 4), np.float64)
         for dz in (0, 1):
             for dy in (0, 1):
                 for dx in (0, 1):
-                    w = ((fr[:, 0] if dx else 1 - fr[:, 0]) * (fr[:, 1] if dy else 1 - fr[:, 1]) * (fr[:, 2] if dz else 1 - fr[:, 2]))
-                    out += w[:, None].astype(np.float64) * texels[i[:, 2] + dz, i[:, 1] + dy, i[:, 0] + dx]
+                    k = (w[:, 0] if dx else 1 - w[:, 0]) * (w[:, 1] if dy else 1 - w[:, 1]) * (w[:, 2] if dz else 1 - w[:, 2])
+                    out += k[:, None] * texels[i[:, 2] + dz, i[:, 1] + dy, i[:, 0] + dx]
         return out
     scale = np.abs(texels).reshape(-1, 4).max(axis=0)
-    e_exact = float((np.abs(hw - blend(False)) / scale).max())
-    e_fixed = float((np.abs(hw - blend(True)) / scale).max())
-    print("tex3D vs exact-fraction blend: %.3e of full scale; vs 8-bit-fraction blend: %.3e" % (e_exact, e_fixed))
-    assert e_fixed < 2e-5 and e_exact > 10 * e_fixed                     # 8 fractional bits explain the unit; exact weights do not
+    e_exact = np.abs(hw - blend(fr)) / scale
+    e_fixed = np.abs(hw - blend(np.floor(fr * 256.0 + 0.5) / 256.0)) / scale
+    print("tex3D, 1-D probe: vs exact fractions %.2e, vs round(frac*256)/256 %.2e of full scale" % (e_exact[:2048].max(), e_fixed[:2048].max()))
+    print("tex3D, 3-D probe: vs exact fractions max %.2e mean %.2e, vs 8-bit fractions max %.2e mean %.2e" % (
+        e_exact[2048:].max(), e_exact[2048:].mean(), e_fixed[2048:].max(), e_fixed[2048:].mean()))
+    assert e_fixed[:2048].max() < 2e-6 and e_exact[:2048].max() > 1e-3       # one axis: exactly 8 fractional bits, round to nearest
+    assert e_fixed[2048:].max() < 8e-3 and e_fixed[2048:].mean() < e_exact[2048:].mean()
