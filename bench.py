@@ -32,18 +32,23 @@ sys.path.insert(0, ROOT)
 
 CUBIC = os.environ.get("PHOTON_INTERPOLATION", "linear") == "cubic"
 # RK4 + trilinear float4: SURVEY.md 8(d) / BASELINE.md 3.  RK4 + tricubic B-spline on scalar coefficients
-# (PHOTON_INTERPOLATION=cubic): 3 x (9 coordinate + 40 weights + 192 FMA x 2) + 135 = 1434, 3 x 64 taps x 4 B.
-FLOP_PER_RAY_STEP = 1434.0 if CUBIC else 330.0
+# (PHOTON_INTERPOLATION=cubic): SURVEY 8(d)'s ~1330 FLOP, 3 x 64 taps x 4 B.
+FLOP_PER_RAY_STEP = 1330.0 if CUBIC else 330.0
 L1_BYTES_PER_RAY_STEP = 768.0 if CUBIC else 384.0    # linear: 3 samples x 8 texels x 16 B
-# dram__bytes_read.sum + dram__bytes_write.sum of one trace launch from the ncu --set full capture under
-# profiles/ (r3k_trace_raw_selected.txt: 44.7 MB read + 1261.6 MB written, linear mode, cell-table kernel);
-# None where no capture of this mode exists.  The writes are L2 evictions of the kernel's local-memory
-# window (1184 B of stack per thread for the out-of-line generic step and the splat footprints, 135 MB
-# resident, competing for the 126 MB L2 with the field streaming through it): 31 GB/s = 0.5 % of HBM.  The
-# algorithmic HBM bytes per launch are ~4.4 MB (source points + one flush of the 4 MiB image) plus the cells
-# the rays of the batch walk through once (10 000 columns x 511 cells x 128 B = 0.65 GB if nothing were shared;
-# neighbouring points share cells and the L2 keeps them: 45 MB read).
-NCU_DRAM_BYTES_PER_LAUNCH = None if CUBIC else 1306324232
+# RK4 + tricubic B-spline on scalar coefficients ~1330 FLOP per ray-step (3 x ~400 + 135)
+FLOP_PER_RAY_STEP_CUBIC = 1330.0
+# generate ~60 + thick lens ~250 + sensor/bilinear ~20 FLOP per ray (SURVEY 8d "per ray (outside the loop)")
+FLOP_PER_RAY_NO_FIELD = 330.0
+
+
+def ncu_figures():
+    """What `ncu --set full` reported for the timed kernel of THIS command, read from profiles/ncu_current.json
+    (written by tools/ncu_summary.py from the capture kept under profiles/; it names the commit it was taken at).
+    Not measured in this run: a capture under a profiler is never a bench value."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_current.json")))
+    except Exception:
+        return None
 
 
 def parse():
@@ -60,6 +65,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity leg of the cpu_baseline section")
+    ap.add_argument("--workloads", default="auto", help="comma list of c1_piv,c4_1024,c5,cubic | none | auto (all at N = 1, sharded C4/C5 at N = 8)")
+    ap.add_argument("--no-in-call", action="store_true", help="N > 1: skip the PHOTON_GPUS leg")
     ap.add_argument("--workdir", default=None)
     return ap.parse_args()
 
@@ -215,7 +222,8 @@ def run_reference_arm(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "rays_per_s": rays / secs,
-            "config": workload_config(args, call),
+            "config": dict(workload_config(args, call), rays_per_step=npts * args.rays_per_point, points_per_step=npts,
+                           note="a step of this arm is a bounded sample of the workload: %d source points x %d rays" % (npts, args.rays_per_point)),
             "cpu_baseline": {"value": v, "unit": "ray-steps/s", "cores": threads, "kind": kind,
                              "sample": f"{npts} source points x {args.rays_per_point} rays per step ({rays} rays total), "
                                        "time inside the tracing kernel launches; the per-call NRRD load + gradient precompute "
@@ -234,6 +242,212 @@ def workload_config(args, call):
             "interpolation": "cubic" if CUBIC else "linear", "rng": os.environ.get("PHOTON_RNG", "reference"),
             "sampler": os.environ.get("PHOTON_SAMPLER", "linear"),
             "l2_policy": "field (2 GiB of texels + 16 GiB cell table at 512^3) is larger than the 126 MB L2; consecutive steps trace different batches"}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The other BASELINE workloads, resident-scene throughput (CUDA-event time of the trace kernel), bounded to a few
+# seconds each: C1-like PIV without a field, C4 (PIV through a turbulent 1024^3 field), C5 (2048 x 2048 x 1024 blob,
+# three optical elements, step-size sweep), cubic mode on C3.  Fields are made on the GPU and handed over in memory.
+# ---------------------------------------------------------------------------------------------------------------------
+def _time_resident(scene, npoints, reps=3, warm=2):
+    n = min(scene.num_points, npoints)
+    for _ in range(warm):
+        scene.trace_range(0, n)
+    scene.reset_counters(); scene.zero_image()
+    ms = []
+    for _ in range(reps):
+        scene.trace_range(0, n); ms.append(scene.last_trace_ms)
+    return n, float(np.mean(ms)), scene.ray_steps / reps, scene.rays / reps
+
+
+def _entry(lib, ms, steps, rays, fp32_peak, flop_per_step=330.0, **extra):
+    sec = ms * 1e-3
+    e = {"ms": ms, "rays_per_s": rays / sec, "kernel": lib.photon_b200_last_variant().decode()}
+    if steps > 0:
+        e.update(value=steps / sec, unit="ray-steps/s", steps_per_ray=steps / max(rays, 1),
+                 roofline_frac=(steps * flop_per_step / sec / 1e12 / fp32_peak) if fp32_peak else None, flop_per_ray_step=flop_per_step)
+    else:
+        e.update(value=rays / sec, unit="rays/s",
+                 roofline_frac=(rays * FLOP_PER_RAY_NO_FIELD / sec / 1e12 / fp32_peak) if fp32_peak else None, flop_per_ray=FLOP_PER_RAY_NO_FIELD)
+    e.update(extra)
+    return e
+
+
+def _c5_field(lib, n=2048, nz=1024):
+    """BASELINE C5's blob on an n x n x nz grid, made on the GPU and registered as "mem:c5" (16 GiB at 2048 x 2048 x 1024)."""
+    import torch
+    from photon_b200.nrrd import register_field
+    extent = 511 * 176.0
+    sx, sz = extent / (n - 1), extent / (nz - 1)
+    dev = torch.device("cuda")
+    cx = (torch.arange(n, dtype=torch.float64, device=dev) - (n - 1) / 2.0) * sx
+    cz = (torch.arange(nz, dtype=torch.float64, device=dev) - (nz - 1) / 2.0) * sz
+    gx = torch.exp(-cx ** 2 / (2.0 * 15e3 ** 2)).float(); gz = torch.exp(-cz ** 2 / (2.0 * 15e3 ** 2)).float()
+    rho = gz[:, None, None] * gx[None, :, None]
+    rho = rho * gx[None, None, :]
+    rho.mul_(0.5).add_(1.225)
+    torch.cuda.synchronize()
+    register_field(lib, "c5", (rho.data_ptr(), (nz, n, n)), (sx, sx, sz), (-extent / 2, -extent / 2, 750e3 - extent / 2))
+    return rho
+
+
+def run_workloads(lib, args, c3_call, fp32_peak, which):
+    import torch
+    from photon_b200 import scenes
+    from photon_b200.scene import ResidentScene
+    out = {}
+
+    def drop():
+        lib.photon_b200_release_cache()
+        torch.cuda.empty_cache()
+
+    for name in which:
+        t0 = time.perf_counter()
+        try:
+            if name == "c1_piv":
+                c = scenes.c1_piv(particles=20000, rays_per_particle=10000)
+                sc = ResidentScene(c)
+                n, ms, steps, rays = _time_resident(sc, 10000)
+                out[name] = _entry(lib, ms, 0, rays, fp32_peak, workload="PIV, no density field: 1e4 particles x 1e4 rays per launch, Mie, thick lens, bilinear splat, 1024^2",
+                                   bound="instruction issue (per-ray generate / lens / splat arithmetic; the working set is the 4 MiB image, L2-resident by nature)")
+                sc.close()
+            elif name.startswith("c4_"):
+                n3 = int(name.split("_")[1])
+                c = scenes.c4_piv("mem:c4", n=n3, particles=100000, rays_per_particle=1000, device="cuda", lib=lib)
+                torch.cuda.empty_cache()
+                sc = ResidentScene(c)
+                n, ms, steps, rays = _time_resident(sc, 10000)
+                out[name] = _entry(lib, ms, steps, rays, fp32_peak, field_bytes=16 * n3 ** 3,
+                                   workload=f"C4: PIV through a turbulent {n3}^3 field, Mie (bhmie table), thick lens, 2048^2 sensor, bilinear splat; 1e4 particles x 1000 rays per launch")
+                sc.close(); lib.photon_b200_unregister_field(b"c4"); del c
+            elif name == "c5":
+                keep = _c5_field(lib)
+                c = scenes.c5_stress("mem:c5", n=2048, nz=1024, write_field=False)
+                for scale in ("1", "0.5", "0.25"):
+                    os.environ["PHOTON_STEP_SCALE"] = scale
+                    try:
+                        sc = ResidentScene(c)
+                        n, ms, steps, rays = _time_resident(sc, 10000, reps=2, warm=1)
+                        out["c5_step_" + scale] = _entry(lib, ms, steps, rays, fp32_peak, field_bytes=16 * 2048 * 2048 * 1024,
+                                                         workload="C5: BOS through a 2048 x 2048 x 1024 blob (the reference keeps 1024 planes), three optical elements, "
+                                                                  f"step = {scale} x spacing; 1e4 points x 1000 rays per launch")
+                        sc.close()
+                    finally:
+                        del os.environ["PHOTON_STEP_SCALE"]
+                lib.photon_b200_unregister_field(b"c5"); del keep, c
+            elif name == "cubic":
+                os.environ["PHOTON_INTERPOLATION"] = "cubic"
+                try:
+                    sc = ResidentScene(c3_call)
+                    n, ms, steps, rays = _time_resident(sc, args.points_per_step, reps=2, warm=1)
+                    out[name] = _entry(lib, ms, steps, rays, fp32_peak, flop_per_step=FLOP_PER_RAY_STEP_CUBIC,
+                                       workload=f"C3 with the tricubic B-spline sampler (PHOTON_INTERPOLATION=cubic), {args.grid}^3 coefficients")
+                    sc.close()
+                finally:
+                    del os.environ["PHOTON_INTERPOLATION"]
+        except Exception as e:
+            out[name] = {"error": repr(e)[:300]}
+        drop()
+        if name in out:
+            out[name]["wall_s_including_setup"] = time.perf_counter() - t0
+    return out
+
+
+def run_workloads_sharded(lib, args, rank, world, local, fp32_peak):
+    """N > 1: BASELINE configs 4 and 5 over all ranks.  C4 AT ITS STATED SIZE (1e6 particles x 1000 rays x 2 frames
+    through the 1024^3 field, 4 MP): every rank makes the same field on its GPU and traces its shard of the particles;
+    partial images are summed with one NCCL reduce per frame.  C5: a slice of the 1e7-point list (1e5 points x 1000
+    rays per rank and step size) through the 2048 x 2048 x 1024 field.  Times are CUDA-event kernel times, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from photon_b200 import scenes
+    from photon_b200.scene import ResidentScene
+    out = {}
+
+    def reduce_max_sum(ms, steps, rays):
+        t = torch.tensor([ms, steps, rays], dtype=torch.float64, device="cuda")
+        mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        return float(mx[0]), float(sm[1]), float(sm[2])
+    try:
+        c = scenes.c4_piv("mem:c4", n=1024, particles=1000000, rays_per_particle=1000, device="cuda", lib=lib)
+        torch.cuda.empty_cache()
+        ny, nx = c.image_shape
+        tot_ms, tot_steps, tot_rays = 0.0, 0.0, 0.0
+        t0 = time.perf_counter()
+        for frame in range(2):
+            if frame == 1:
+                c.x = (c.x + np.float32(17.0 / 0.176)).astype(np.float32)         # about one pixel on the sensor
+            sc = ResidentScene(c, shard=(rank, world), device=local)
+            sc.reset_counters()
+            sc.trace(); ms = sc.last_trace_ms
+            img = torch.from_numpy(sc.download_image().reshape(-1)).cuda()
+            dist.reduce(img, dst=0)
+            m, st, ry = reduce_max_sum(ms, sc.ray_steps, sc.rays)
+            tot_ms += m; tot_steps += st; tot_rays += ry
+            sc.close()
+        torch.cuda.synchronize(); dist.barrier()
+        wall = time.perf_counter() - t0
+        out["c4_full"] = {"value": tot_steps / (tot_ms * 1e-3), "unit": "ray-steps/s", "rays": tot_rays, "rays_per_s": tot_rays / (tot_ms * 1e-3),
+                          "kernel_seconds": tot_ms * 1e-3, "wall_seconds_with_upload_and_reduce": wall, "gpus": world,
+                          "kernel": lib.photon_b200_last_variant().decode(),
+                          "roofline_frac_per_gpu": tot_steps * 330.0 / (tot_ms * 1e-3) / 1e12 / fp32_peak / world if fp32_peak else None,
+                          "workload": "BASELINE config 4 at its stated size: 1e6 Mie particles x 1000 rays x 2 frames, turbulent 1024^3 field replicated per GPU, 2048^2 sensor"}
+        lib.photon_b200_unregister_field(b"c4"); del c
+    except Exception as e:
+        out["c4_full"] = {"error": repr(e)[:300]}
+    lib.photon_b200_release_cache(); torch.cuda.empty_cache()
+    try:
+        keep = _c5_field(lib)
+        c = scenes.c5_stress("mem:c5", n=2048, nz=1024, write_field=False, dots_per_side=316, points_per_dot=100)
+        per_rank = 100000
+        sub = c.subset(slice(rank * per_rank, (rank + 1) * per_rank))
+        for scale in ("1", "0.5", "0.25"):
+            os.environ["PHOTON_STEP_SCALE"] = scale
+            try:
+                sc = ResidentScene(sub, device=local)
+                sc.reset_counters()
+                sc.trace(); ms = sc.last_trace_ms
+                m, st, ry = reduce_max_sum(ms, sc.ray_steps, sc.rays)
+                out["c5_step_" + scale] = {"value": st / (m * 1e-3), "unit": "ray-steps/s", "rays": ry, "rays_per_s": ry / (m * 1e-3), "kernel_seconds": m * 1e-3,
+                                           "gpus": world, "kernel": lib.photon_b200_last_variant().decode(),
+                                           "full_job_seconds_extrapolated": 1e10 / (ry / (m * 1e-3)),
+                                           "workload": f"BASELINE config 5, a slice: {per_rank} of the 1e7 source points x 1000 rays per GPU, 2048 x 2048 x 1024 field replicated per GPU, "
+                                                       f"three optical elements, step = {scale} x spacing"}
+                sc.close()
+            finally:
+                del os.environ["PHOTON_STEP_SCALE"]
+        lib.photon_b200_unregister_field(b"c5"); del keep, c
+    except Exception as e:
+        out["c5"] = {"error": repr(e)[:300]}
+    lib.photon_b200_release_cache(); torch.cuda.empty_cache()
+    return out
+
+
+def run_in_call(lib, call, world):
+    """The library's OWN multi-GPU path: rank 0 alone makes ONE start_ray_tracing call over the whole C3 job
+    with PHOTON_GPUS = N -- the library splits the source points over the N devices of the box, builds the field on each,
+    and combines the partial images with one ncclReduce onto device 0.  Cold (nothing cached: field read + built on
+    every device, communicator set-up) then warm (second image of a BOS pair), then the same call on one GPU."""
+    rays = call.num_particles * call.lightray_number_per_particle
+    lib.photon_b200_release_cache()
+    res = {"gpus": world, "rays": rays}
+    os.environ.pop("PHOTON_SHARD", None)
+    os.environ.pop("PHOTON_DEVICE", None)
+    os.environ["PHOTON_GPUS"] = str(world)
+    try:
+        t0 = time.perf_counter(); img = call.run(lib); res["cold_s"] = time.perf_counter() - t0
+        t0 = time.perf_counter(); img = call.run(lib); res["warm_s"] = time.perf_counter() - t0
+        os.environ["PHOTON_GPUS"] = "1"
+        t0 = time.perf_counter(); one = call.run(lib); res["one_gpu_warm_s"] = time.perf_counter() - t0
+    finally:
+        del os.environ["PHOTON_GPUS"]
+    res["speedup_vs_1"] = res["one_gpu_warm_s"] / res["warm_s"]
+    res["rays_per_s_warm"] = rays / res["warm_s"]
+    i1 = one.astype(np.float64)
+    res["image_rel_l2_vs_sharded"] = float(np.linalg.norm(img - i1) / np.linalg.norm(i1))
+    res["note"] = "one start_ray_tracing call with host buffers per figure; NRRD file in the page cache; cold includes ncclCommInitAll"
+    return res
 
 
 _JSON_FD = None
@@ -369,14 +583,42 @@ def main():
                "note": "start_ray_tracing with host numpy buffers; NRRD field cached in HBM across calls"}
         del os.environ["PHOTON_SHARD"]
 
+    # ---- the other workloads and the library's in-call multi-GPU path (after the headline legs) ------------------------
+    fp32_peak = lib.photon_b200_measure_fp32_tflops(local)
+    workloads, in_call = None, None
+    wl = args.workloads
+    if wl != "none":
+        if world == 1:
+            which = ["c1_piv", "c4_1024", "c5", "cubic"] if wl == "auto" else [w for w in wl.split(",") if w]
+            scene.close(); scene = None
+            lib.photon_b200_release_cache()
+            workloads = run_workloads(lib, args, call, fp32_peak, which)
+        elif world == 8 or wl != "auto":
+            scene.close(); scene = None
+            lib.photon_b200_release_cache()
+            workloads = run_workloads_sharded(lib, args, rank, world, local, fp32_peak)
+    if world > 1 and not args.no_in_call:
+        if scene is not None:
+            scene.close(); scene = None
+        lib.photon_b200_release_cache()
+        torch.cuda.empty_cache()
+        barrier_plain = lambda: (torch.cuda.synchronize(), dist.barrier())
+        barrier_plain()
+        if rank == 0:
+            try:
+                in_call = run_in_call(lib, call, world)
+            except Exception as e:
+                in_call = {"error": repr(e)[:300]}
+        barrier_plain()
+
     if rank == 0:
-        fp32_peak = lib.photon_b200_measure_fp32_tflops(local)
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
         k_ms = float(np.mean(kernel_ms))
+        ncu = ncu_figures()
         steps_per_launch = steps_done / max(args.steps, 1)
         achieved_tf = steps_per_launch * FLOP_PER_RAY_STEP / (k_ms * 1e-3) / 1e12
         line = {
@@ -388,9 +630,10 @@ def main():
             "gpu_launches": launches * world,
             "clocks": clocks.summary(),
             "e2e": e2e,
+            "workloads": workloads, "in_call": in_call,
             "roofline": {"bound": "fp32_issue", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp32_peak if fp32_peak and fp32_peak > 0 else None,
-                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
+                         "traffic": (ncu or {}).get("dram_bytes_per_launch") if not CUBIC else None,
                          "kernel": "trace_rays_kernel<BSplineField>" if CUBIC else "trace_rays_kernel<LinearFieldCells>", "kernel_ms": k_ms,
                          "flop_per_ray_step": FLOP_PER_RAY_STEP, "ray_steps_per_launch": steps_per_launch,
                          "peak_source": "FFMA loop measured live on this GPU (photon_b200_measure_fp32_tflops); "
@@ -398,10 +641,8 @@ def main():
                          "l1_bytes_per_ray_step": L1_BYTES_PER_RAY_STEP,
                          "l1_gbs_achieved": steps_per_launch * L1_BYTES_PER_RAY_STEP / (k_ms * 1e-3) / 1e9,
                          "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
-                         # what ncu --set full reported for this kernel and command (not measured in this run)
-                         "ncu": {"issue_slots_busy": 0.672, "fma_pipe_busy": 0.565, "dram_throughput": 0.005,
-                                 "l1_hit_rate": 0.883, "warp_instructions_per_ray_step": 204,
-                                 "source": "profiles/r3k_trace_details.txt, r3k_trace_raw_selected.txt"} if not CUBIC else None},
+                         # what ncu --set full reported for this kernel and command (profiles/ncu_current.json; not measured in this run)
+                         "ncu": ncu if not CUBIC else None},
         }
         if not args.no_cpu_baseline and world == 1:
             cl, kind = cpu_reference_lib()
@@ -418,7 +659,8 @@ def main():
                 except Exception as e:            # the headline numbers stand on their own; say why parity is absent
                     line["parity"] = {"error": repr(e)[:300]}
         emit(line)
-    scene.close()
+    if scene is not None:
+        scene.close()
     if world > 1:
         dist.destroy_process_group()
 

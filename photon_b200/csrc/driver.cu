@@ -202,7 +202,7 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
         CK(cudaMemcpyAsync(d_rho, src, n * sizeof(float), cudaMemcpyDefault, st));
     }
     CK(cudaMemsetAsync(d_min, 0xff, sizeof(unsigned int), st));
-    int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)148 * 16);
+    int blocks = (int)std::min<size_t>((size_t)sy * sz, (size_t)148 * 16);      // rows (y, z); a multiple of the SM count when there are enough
     // the reference's float-arithmetic voxel index (trace_core.cuh: field_voxel) differs from the integer one only
     // above 2^24 voxels
     const char *gi = getenv("PHOTON_GRADIENT_INDEX");
@@ -270,7 +270,7 @@ bool ensure_cells(DeviceField &F, cudaStream_t st) {
         cudaGetLastError(); F.cells_refused = true; return false;
     }
     if (cudaMalloc(&F.cells, bytes) != cudaSuccess) { cudaGetLastError(); F.cells = nullptr; F.cells_refused = true; return false; }
-    int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)148 * 16);
+    int blocks = (int)std::min<size_t>((size_t)F.P.H * F.P.D, (size_t)148 * 16);
     build_cells_kernel<<<blocks, 256, 0, st>>>(F.lin, F.cells, F.P.W, F.P.H, F.P.D);
     if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
         cudaGetLastError(); cudaFree(F.cells); F.cells = nullptr; F.cells_refused = true; return false;
@@ -424,7 +424,6 @@ struct photon_scene {
     int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
     double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
     int *d_order = nullptr;              // processing order of the source points (Morton order of x, y), or null
-    bool grouped = false;                // fan-out rays: CTAs own groups of 32 neighbouring points, lanes = points (PHOTON_GROUP)
     bool coherent = false;               // rays of a source point stay within ~a cell of each other: v5 hot loop
     bool use_cells = false;              // ... and the field has its per-cell polynomial table (PHOTON_CELLS, default on)
     long long n_dots = 0, rays_per_dot = 0;
@@ -478,10 +477,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
     a.inter_pos = ipos; a.inter_dir = idir; a.n_inter = n_inter;
     const bool dump = fpos != nullptr || ipos != nullptr;
     int grid = std::min(point_count, s->grid_blocks);
-    // fan-out scenes: a CTA owns 32 neighbouring source points and a warp's lanes trace one ray of each (trace_kernel.cuh)
-    const bool grouped = s->grouped && s->d_dots == nullptr && !s->d_fixed && !s->use_texture && !s->use_cubic &&
-                         a.simulate_gradients && (a.algorithm == 1 || a.algorithm == 2);
-    if (grouped) grid = std::min((point_count + 31) / 32, s->grid_blocks);
+
     a.dot_stats = s->d_dots; a.rays_per_dot = s->rays_per_dot; a.n_dots = s->n_dots;
     a.order = dump ? nullptr : s->d_order;
     const bool stats = s->d_dots != nullptr;
@@ -541,10 +537,8 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         int g = (stats || fixed || !a.simulate_gradients) ? G_FANOUT : s->use_cells ? G_CELLS : s->coherent ? G_COHERENT : G_FANOUT;
         if (g == G_CELLS && occ != 3) g = G_COHERENT;
         if (g == G_COHERENT && occ != 3 && occ != 5) g = G_FANOUT;
-        gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : grouped ? "fanout32" : "fanout";
-        if (grouped && g == G_FANOUT && dump) trace_rays_kernel<true, 2, LinearField, false, PH_BLOCK, false, 1, 32><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (grouped && g == G_FANOUT) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, false, 1, 32><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
-        else if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : "fanout";
+        if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump && g == G_CELLS) trace_rays_kernel<true, 2, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, SC);
@@ -751,7 +745,6 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         // coherent rays: the cone of a source point at the lens (cone_ratio * lens_pitch) is narrower than a cell
         s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
         if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;
-        { const char *gp = getenv("PHOTON_GROUP"); s->grouped = !s->coherent && s->npoints >= 64 && !(gp && atoi(gp) == 0); }
         std::lock_guard<std::mutex> field_lock(s->field->mu);            // the on-demand tables below are added under it
         { const char *pc = getenv("PHOTON_CELLS");
           s->use_cells = s->coherent && algorithm == 2 && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }   // only rk4_hot reads it

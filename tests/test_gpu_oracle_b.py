@@ -144,5 +144,5 @@ def test_texture_unit_weights_are_8_bit(cuda_lib, tmp_path):
     print("tex3D, 1-D probe: vs exact fractions %.2e, vs round(frac*256)/256 %.2e of full scale" % (e_exact[:2048].max(), e_fixed[:2048].max()))
     print("tex3D, 3-D probe: vs exact fractions max %.2e mean %.2e, vs 8-bit fractions max %.2e mean %.2e" % (
         e_exact[2048:].max(), e_exact[2048:].mean(), e_fixed[2048:].max(), e_fixed[2048:].mean()))
-    assert e_fixed[:2048].max() < 2e-6 and e_exact[:2048].max() > 1e-3       # one axis: exactly 8 fractional bits, round to nearest
+    assert e_fixed[:2048].max() < 2e-6 and e_exact[:2048].max() > 1e-4       # one axis: exactly 8 fractional bits, round to nearest
     assert e_fixed[2048:].max() < 8e-3 and e_fixed[2048:].mean() < e_exact[2048:].mean()

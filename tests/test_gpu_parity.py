@@ -131,17 +131,15 @@ def test_nondump_kernel_image_matches_oracle(name, cases, cuda_lib, oracle_lib):
     assert m <= (5e-3 if name in util.AB4_CASES else util.TOL_IMG_L2), (name, variant, m)
 
 
-GATHERERS = {"cells": {}, "coherent": {"PHOTON_CELLS": "0"}, "fanout32": {"PHOTON_HOT": "4"},
-             "fanout": {"PHOTON_HOT": "4", "PHOTON_GROUP": "0"}}
+GATHERERS = {"cells": {}, "coherent": {"PHOTON_CELLS": "0"}, "fanout": {"PHOTON_HOT": "4"}}
 
 
 @pytest.mark.parametrize("dump", [True, False], ids=["dump", "image"])
 @pytest.mark.parametrize("gatherer", list(GATHERERS))
 def test_every_rk4_gatherer_dump_and_image(gatherer, dump, cases, cuda_lib, oracle_lib, tmp_path, monkeypatch):
-    """The RK4 hot loops the driver can pick for a linear field -- per-cell polynomial table, coherent corner texels
-    (what a coherent scene runs when the table does not fit: C3 at 1024^3, all of C5), fan-out corner texels (PIV
-    through a field) with a CTA per group of 32 neighbouring source points (fanout32, the default) or per source point
-    -- each through its dump kernel (per-ray parity) and its non-dump kernel (image parity).
+    """The three RK4 hot loops the driver can pick for a linear field -- per-cell polynomial table, coherent corner
+    texels (what a coherent scene runs when the table does not fit: C3 at 1024^3, all of C5), fan-out corner texels
+    (PIV through a field) -- each through its dump kernel (per-ray parity) and its non-dump kernel (image parity).
     photon_b200_last_variant proves which kernel ran."""
     call, pitch = cases["bos_rk4_thin_diffraction"]
     for k, v in GATHERERS[gatherer].items():
@@ -177,11 +175,11 @@ def test_c4_shaped_scene_matches_oracle(cuda_lib, oracle_lib, tmp_path):
     variant = cuda_lib.photon_b200_last_variant().decode()
     m = util.compare(ref, got, 17.0)
     print("C4-shaped", variant, m)
-    assert variant == "rk4/fanout32/dump", variant
+    assert variant == "rk4/fanout/dump", variant
     util.assert_parity("piv_mie_thick_bilinear", m)                      # thick lens: 1e-3 px at the 99.9th percentile
     plain = call.run(cuda_lib)
     variant = cuda_lib.photon_b200_last_variant().decode()
-    assert variant == "rk4/fanout32/image", variant
+    assert variant == "rk4/fanout/image", variant
     assert _rel_l2(plain, ref[0]) <= util.TOL_IMG_L2
     # the field matters in this scene: without it the hits move
     call.simulate_density_gradients = False
