@@ -435,6 +435,7 @@ def run_in_call(lib, call, world):
     os.environ.pop("PHOTON_SHARD", None)
     os.environ.pop("PHOTON_DEVICE", None)
     os.environ["PHOTON_GPUS"] = str(world)
+    os.environ["PHOTON_TIMING"] = "1"                 # the library's own per-stage laps go to stderr (kept by the driver's log)
     try:
         t0 = time.perf_counter(); img = call.run(lib); res["cold_s"] = time.perf_counter() - t0
         t0 = time.perf_counter(); img = call.run(lib); res["warm_s"] = time.perf_counter() - t0
@@ -442,6 +443,7 @@ def run_in_call(lib, call, world):
         t0 = time.perf_counter(); one = call.run(lib); res["one_gpu_warm_s"] = time.perf_counter() - t0
     finally:
         del os.environ["PHOTON_GPUS"]
+        os.environ.pop("PHOTON_TIMING", None)
     res["speedup_vs_1"] = res["one_gpu_warm_s"] / res["warm_s"]
     res["rays_per_s_warm"] = rays / res["warm_s"]
     i1 = one.astype(np.float64)
@@ -488,8 +490,13 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # a CPU-side group for the waits around the in-call leg: an NCCL barrier is a kernel that SPINS on the waiting
+        # rank's GPU, and the library's in-call path runs its shards on those same GPUs from rank 0's process --
+        # two processes on one GPU are time-sliced, which halved the in-call rate in the first run (profiles r4f)
+        cpu_group = dist.new_group(backend="gloo")
     workdir = args.workdir or os.path.join(tempfile.gettempdir(), "photon_bench")
     os.makedirs(workdir, exist_ok=True)
     if rank == 0:
@@ -602,14 +609,14 @@ def main():
             scene.close(); scene = None
         lib.photon_b200_release_cache()
         torch.cuda.empty_cache()
-        barrier_plain = lambda: (torch.cuda.synchronize(), dist.barrier())
-        barrier_plain()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)                   # every GPU idle, nobody spinning on one
         if rank == 0:
             try:
                 in_call = run_in_call(lib, call, world)
             except Exception as e:
                 in_call = {"error": repr(e)[:300]}
-        barrier_plain()
+        dist.barrier(group=cpu_group)
 
     if rank == 0:
         peaks = {}

@@ -37,6 +37,7 @@
  *   PHOTON_NCCL=0           PHOTON_GPUS: sum the partial images through the host instead of one ncclReduce
  *   PHOTON_STEP_SCALE=<k>   integrator step = k x smallest grid spacing (the reference has k = 1 only)
  *   PHOTON_FULL_DEPTH=1     keep more than the 1024 z-planes the reference keeps (trace.h:2037-2038)
+ *   PHOTON_INDEX64=1        run the 64-bit-voxel-index hot loop (automatic above 2^32 voxels, e.g. 2048^3 with PHOTON_FULL_DEPTH)
  *   PHOTON_CELLS=<0|1>      coherent RK4 loop reads the per-cell polynomial table (128 B per voxel) [default 1 when it fits]
  *   PHOTON_CELLS_MAX_GIB=<g>  largest table that is built [default 40]; beyond it the loop reads the corner texels
  *   PHOTON_NO_FIELD_CACHE=1 rebuild the density field on every call

@@ -180,8 +180,10 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
     step = step < dz ? step : (float)dz;
     P.step = step;
     size_t n = (size_t)sx * sy * sz;
-    if (n > ((size_t)1 << 32)) {         // the sampler indexes voxels with 32 bits (ray_stages.cuh): indices 0 .. 2^32-1
-        g_error = "density field has more than 2^32 voxels; not supported by this build";
+    // Up to 2^32 voxels the hot loops index voxels with 32 bits; beyond (2048^3 with PHOTON_FULL_DEPTH: 128 GiB of
+    // texels) the scene runs the 64-bit-index instantiation (LinearFieldWide, ray_stages.cuh).
+    if (n > ((size_t)1 << 34)) {
+        g_error = "density field has more than 2^34 voxels; not supported by this build";
         fprintf(stderr, "libparallel_ray_tracing(b200): %s\n", g_error.c_str());
         return false;
     }
@@ -424,6 +426,7 @@ struct photon_scene {
     int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
     double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
     int *d_order = nullptr;              // processing order of the source points (Morton order of x, y), or null
+    bool wide = false;                   // field of more than 2^32 voxels (or PHOTON_INDEX64=1): 64-bit voxel index in the hot loop
     bool coherent = false;               // rays of a source point stay within ~a cell of each other: v5 hot loop
     bool use_cells = false;              // ... and the field has its per-cell polynomial table (PHOTON_CELLS, default on)
     long long n_dots = 0, rays_per_dot = 0;
@@ -530,7 +533,10 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         LinearFieldCells SC; static_cast<LinearField &>(SC) = S; SC.cells = s->use_cells ? s->field->cells : nullptr;
         LinearFieldCoherent SH; static_cast<LinearField &>(SH) = S;
+        LinearFieldWide SW; static_cast<LinearField &>(SW) = S;
         const bool fixed = s->d_fixed != nullptr;
+        const bool wide = s->wide && a.simulate_gradients;
+        if (wide && (stats || fixed)) { g_error = "dot statistics / PHOTON_DETERMINISTIC are not available for fields of more than 2^32 voxels"; return false; }
         // the gatherer of the scene (what the non-dump launch runs; PHOTON_OCC variants exist for some only)
         enum { G_FANOUT, G_COHERENT, G_CELLS };
         const int occ = s->occupancy;
@@ -538,7 +544,10 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         if (g == G_CELLS && occ != 3) g = G_COHERENT;
         if (g == G_COHERENT && occ != 3 && occ != 5) g = G_FANOUT;
         gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : "fanout";
-        if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        if (wide) gat = "wide";
+        if (wide && dump) trace_rays_kernel<true, 2, LinearFieldWide><<<grid, PH_BLOCK, 0, s->stream>>>(a, SW);
+        else if (wide) trace_rays_kernel<false, 3, LinearFieldWide><<<grid, PH_BLOCK, 0, s->stream>>>(a, SW);
+        else if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (fixed) trace_rays_kernel<false, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump && g == G_CELLS) trace_rays_kernel<true, 2, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, SC);
@@ -746,8 +755,10 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         s->coherent = rpp == 1 || cone_ratio * lens_pitch < a.field.step;
         if (const char *h = getenv("PHOTON_HOT")) s->coherent = atoi(h) >= 5;
         std::lock_guard<std::mutex> field_lock(s->field->mu);            // the on-demand tables below are added under it
+        { const char *w = getenv("PHOTON_INDEX64");
+          s->wide = (size_t)a.field.W * a.field.H * a.field.D > ((size_t)1 << 32) || (w && atoi(w) != 0); }
         { const char *pc = getenv("PHOTON_CELLS");
-          s->use_cells = s->coherent && algorithm == 2 && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }   // only rk4_hot reads it
+          s->use_cells = !s->wide && s->coherent && algorithm == 2 && !(pc && atoi(pc) == 0) && ensure_cells(*s->field, s->stream); }   // only rk4_hot reads it
         const char *smp = getenv("PHOTON_SAMPLER");
         s->use_texture = smp && strcmp(smp, "texture") == 0;
         if (s->use_texture && !ensure_texture(*s->field, s->stream)) return false;

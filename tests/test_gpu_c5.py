@@ -69,3 +69,28 @@ def test_step_scale_halves_the_step(c5, monkeypatch):
         assert np.isfinite(img).all() and img.sum() > 0
         s.close()
     assert 1.9 < steps["0.5"] / steps["1"] < 2.1, steps
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("alg", [2, 1])
+def test_wide_index_hot_loop_equals_the_32_bit_one(alg, cuda_lib, tmp_path, monkeypatch):
+    """Fields of more than 2^32 voxels (BASELINE C5 at its full 2048^3 with PHOTON_FULL_DEPTH: 128 GiB of texels) run
+    the 64-bit-voxel-index instantiation of the coherent hot loop.  An oracle run at that size is not affordable, so the
+    instantiation is forced (PHOTON_INDEX64=1) on a field that fits both: same texels, same arithmetic, only the width
+    of the index -- ray dumps and image must be bit-identical."""
+    from photon_b200 import scenes
+    call = scenes.c3_bos(str(tmp_path / "blob.nrrd"), n=64, dots_per_side=8, points_per_dot=8, rays_per_point=40, algorithm=alg)
+    monkeypatch.setenv("PHOTON_CELLS", "0")
+    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
+    narrow = util.run_with_dumps(cuda_lib, call, str(tmp_path / "a"))
+    v0 = cuda_lib.photon_b200_last_variant().decode()
+    monkeypatch.setenv("PHOTON_INDEX64", "1")
+    wide = util.run_with_dumps(cuda_lib, call, str(tmp_path / "b"))
+    v1 = cuda_lib.photon_b200_last_variant().decode()
+    assert v0.endswith("/coherent/dump") and v1.endswith("/wide/dump"), (v0, v1)
+    assert np.array_equal(narrow[1], wide[1], equal_nan=True) and np.array_equal(narrow[2], wide[2], equal_nan=True)
+    img0 = call.run(cuda_lib)
+    assert cuda_lib.photon_b200_last_variant().decode().endswith("/wide/image")
+    monkeypatch.delenv("PHOTON_INDEX64")
+    img1 = call.run(cuda_lib)
+    assert float(np.linalg.norm(img0.astype(np.float64) - img1) / np.linalg.norm(img1.astype(np.float64))) <= 1e-6

@@ -21,8 +21,10 @@ call = scenes.c3_bos(nrrd, n=args.grid, dots_per_side=100, points_per_dot=100, r
                      write_field=not os.path.exists(nrrd))
 lib = load_library(require_gpu=True)
 rays = call.num_particles * call.lightray_number_per_particle
+# the N the library will really use: PHOTON_GPUS as the library reads it (set above from --gpus, or by the caller), capped by the box
+gpus_used = max(1, min(int(os.environ.get("PHOTON_GPUS", "1")), lib.photon_b200_device_count()))
 out = {"workload": f"C3 {args.grid}^3, {call.num_particles} source points x {call.lightray_number_per_particle} rays = {rays:.3e} rays, one start_ray_tracing call",
-       "gpus": args.gpus}
+       "gpus": gpus_used, "gpus_requested": args.gpus}
 for tag in ("cold", "warm"):
     t0 = time.perf_counter()
     img = call.run(lib)
