@@ -87,16 +87,19 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index=0):
+        # index: one GPU ordinal, or "all" (rows then carry every GPU of the box, one line each)
         self.index, self.rows, self.stop = index, [], threading.Event()
         self.t = threading.Thread(target=self.run, daemon=True)
 
     def run(self):
         while not self.stop.is_set():
             try:
-                o = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
-                                    str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if o:
-                    self.rows.append([t.strip() for t in o.split(",")])
+                sel = [] if self.index == "all" else ["-i", str(self.index)]
+                o = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"] + sel,
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                for ln in o.splitlines():
+                    if ln.strip():
+                        self.rows.append([t.strip() for t in ln.split(",")])
             except Exception:
                 pass
             self.stop.wait(0.2)
@@ -438,7 +441,9 @@ def run_in_call(lib, call, world):
     os.environ["PHOTON_TIMING"] = "1"                 # the library's own per-stage laps go to stderr (kept by the driver's log)
     try:
         t0 = time.perf_counter(); img = call.run(lib); res["cold_s"] = time.perf_counter() - t0
-        t0 = time.perf_counter(); img = call.run(lib); res["warm_s"] = time.perf_counter() - t0
+        with ClockSampler("all") as ck:               # a multi-second kernel on every GPU at once: are the clocks held?
+            t0 = time.perf_counter(); img = call.run(lib); res["warm_s"] = time.perf_counter() - t0
+        res["clocks_warm"] = ck.summary()
         os.environ["PHOTON_GPUS"] = "1"
         t0 = time.perf_counter(); one = call.run(lib); res["one_gpu_warm_s"] = time.perf_counter() - t0
     finally:

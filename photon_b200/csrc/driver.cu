@@ -67,13 +67,14 @@ struct DeviceField {
     f3 spacing{};
     f4 *lin = nullptr;                   // [D][H][W] float4 (grad n, n-1)
     float *coef = nullptr;               // cubic mode: [D][H][W] B-spline coefficients of n-1 (built on demand)
+    float4 *coefq = nullptr;             // ... and their quad rows (c[x..x+3] per voxel) for the cubic hot loop
     float4 *cells = nullptr;             // coherent hot loop: [D][H][W][8] per-cell polynomial table (built on demand)
     bool cells_refused = false;          // it did not fit; do not try again for this field
     cudaArray_t arr = nullptr;           // optional 3-D array for the texture path
     cudaTextureObject_t tex = 0;
     size_t bytes() const {
         const size_t n = (size_t)P.W * P.H * P.D;
-        return (lin ? n * 16 : 0) + (coef ? n * 4 : 0) + (cells ? n * 128 : 0) + (arr ? n * 16 : 0);
+        return (lin ? n * 16 : 0) + (coef ? n * 4 : 0) + (coefq ? n * 16 : 0) + (cells ? n * 128 : 0) + (arr ? n * 16 : 0);
     }
     void release() {
         if (device >= 0) cudaSetDevice(device);
@@ -81,8 +82,9 @@ struct DeviceField {
         if (arr) cudaFreeArray(arr);
         if (lin) cudaFree(lin);
         if (coef) cudaFree(coef);
+        if (coefq) cudaFree(coefq);
         if (cells) cudaFree(cells);
-        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; cells = nullptr; cells_refused = false;
+        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; coefq = nullptr; cells = nullptr; cells_refused = false;
     }
 };
 // The field cache.  An entry is keyed by (device, path, mtime, size) and REFERENCE COUNTED: every scene (and every
@@ -254,6 +256,12 @@ bool ensure_coefficients(DeviceField &F, cudaStream_t st) {
         prefilter_kernel<<<b, 128, 0, st>>>(F.coef, F.P.W, F.P.H, F.P.D, axis);
     }
     CK(cudaGetLastError());
+    // quad rows for the hot loop (16 B per voxel); without them (out of memory) every step takes the generic path
+    if (cudaMalloc(&F.coefq, n * sizeof(float4)) == cudaSuccess) {
+        const size_t rows = (size_t)F.P.H * F.P.D;
+        quad_rows_kernel<<<(unsigned)std::min<size_t>(rows, (size_t)148 * 16), 256, 0, st>>>(F.coef, F.coefq, F.P.W, rows);
+        CK(cudaGetLastError());
+    } else { cudaGetLastError(); F.coefq = nullptr; }
     CK(cudaStreamSynchronize(st));
     return true;
 }
@@ -501,7 +509,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         gat = s->use_cubic ? "cubic" : s->use_texture ? "texture" : "generic";
         LinearField S; S.g = s->field ? s->field->lin : nullptr; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         if (s->use_cubic) {
-            BSplineField B; B.c = s->field->coef; B.W = a.field.W; B.H = a.field.H; B.D = a.field.D;
+            BSplineField B; B.c = s->field->coef; B.quad = s->field->coefq; B.W = a.field.W; B.H = a.field.H; B.D = a.field.D;
             B.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
             if (dump) trace_rays_kernel<true, 2, BSplineField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, B);
             else trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, B);
@@ -518,7 +526,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         }
     } else if (s->use_cubic) {
         gat = "cubic";
-        BSplineField S; S.c = s->field->coef; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
+        BSplineField S; S.c = s->field->coef; S.quad = s->field->coefq; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         S.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
         if (stats) trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump) trace_rays_kernel<true, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
@@ -1111,7 +1119,7 @@ int photon_b200_sample_field(const char *path, int cubic, int n, const float *xy
             TextureField S; S.tex = F->tex;
             sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
         } else if (cubic) {
-            BSplineField S; S.c = F->coef; S.W = F->P.W; S.H = F->P.H; S.D = F->P.D;
+            BSplineField S; S.c = F->coef; S.quad = F->coefq; S.W = F->P.W; S.H = F->P.H; S.D = F->P.D;
             S.inv_sp = mk3(1.0f / F->spacing.x, 1.0f / F->spacing.y, 1.0f / F->spacing.z);
             sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
         } else {
@@ -1356,11 +1364,17 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
     std::thread nccl_init([ngpus]() { nccl_prepare(ngpus); });
     for (int g = 0; g < ngpus; g++) {
         th.emplace_back([&, g]() {
+            auto t0 = std::chrono::steady_clock::now();
             photon_scene *s = make_scene(shard_index * ngpus + g, shard_count * ngpus, g);
             if (!s) return;
+            auto t1 = std::chrono::steady_clock::now();
             res[g].scene = s;
             res[g].ok = (g != 0 || photon_scene_upload_image(s, image_array) == 0)     // accumulate onto the caller's image
                         && photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
+            if (timing) fprintf(stderr, "[photon timing] gpu %d: scene + field %8.3f ms, trace %8.3f ms (kernel %8.3f ms)\n", g,
+                                std::chrono::duration<double, std::milli>(t1 - t0).count(),
+                                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count(),
+                                (double)photon_scene_last_trace_ms(s));
         });
     }
     for (auto &t : th) t.join();
