@@ -509,7 +509,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         gat = s->use_cubic ? "cubic" : s->use_texture ? "texture" : "generic";
         LinearField S; S.g = s->field ? s->field->lin : nullptr; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         if (s->use_cubic) {
-            BSplineField B; B.c = s->field->coef; B.quad = s->field->coefq; B.W = a.field.W; B.H = a.field.H; B.D = a.field.D;
+            BSplineField B; B.c = s->field->coef; B.quad = reinterpret_cast<const f4 *>(s->field->coefq); B.W = a.field.W; B.H = a.field.H; B.D = a.field.D;
             B.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
             if (dump) trace_rays_kernel<true, 2, BSplineField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, B);
             else trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, false, 2><<<grid, PH_BLOCK, 0, s->stream>>>(a, B);
@@ -526,7 +526,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         }
     } else if (s->use_cubic) {
         gat = "cubic";
-        BSplineField S; S.c = s->field->coef; S.quad = s->field->coefq; S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
+        BSplineField S; S.c = s->field->coef; S.quad = reinterpret_cast<const f4 *>(s->field->coefq); S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         S.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
         if (stats) trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump) trace_rays_kernel<true, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
@@ -1119,7 +1119,7 @@ int photon_b200_sample_field(const char *path, int cubic, int n, const float *xy
             TextureField S; S.tex = F->tex;
             sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
         } else if (cubic) {
-            BSplineField S; S.c = F->coef; S.quad = F->coefq; S.W = F->P.W; S.H = F->P.H; S.D = F->P.D;
+            BSplineField S; S.c = F->coef; S.quad = reinterpret_cast<const f4 *>(F->coefq); S.W = F->P.W; S.H = F->P.H; S.D = F->P.D;
             S.inv_sp = mk3(1.0f / F->spacing.x, 1.0f / F->spacing.y, 1.0f / F->spacing.z);
             sample_field_kernel<<<blocks, 128, 0, st>>>(S, n, d_in, d_out);
         } else {

@@ -155,18 +155,27 @@ PH_HD SensorSample trace_one(const TraceArgs &a, const Sampler &S, int p, int lr
 // rounded away (at 512^3, x +- 1 lands on a multiple of 8 and the x gradient of most voxels is 0 or 4x too large).
 // Reproduced by default for fields of more than 2^24 voxels (parity with the reference's images); an index rounded
 // past the end (the reference reads out of bounds) is clamped.  PHOTON_GRADIENT_INDEX=exact selects the integer index.
+// The index arithmetic lives in an Indexer so that the ingest kernel can hoist what is constant along a row:
+//   VoxelIndex<false>  integer index;
+//   VoxelIndex<true>   the reference's float index, every term evaluated per call (host check, oracle-style);
+//   RowIndex           the same float index with fl(fl(z W) H) + fl(y W) precomputed for the five (y, z) pairs an
+//                      interior voxel touches (trace_kernel.cuh) -- the same operations on the same operands, so the
+//                      same bits.
 template <bool FLOAT_INDEX>
-PH_HD f4 field_voxel(const float *rho, int x, int y, int z, int W, int H, int D, float gx, float gy, float gz) {
-    const float K = 0.225e-3f;
-    const size_t sW = (size_t)W, sWH = (size_t)W * (size_t)H, n = sWH * (size_t)D;
-    const float fW = (float)W, fH = (float)H;
-    auto idx = [&](int xx, int yy, int zz) -> size_t {
-        if (!FLOAT_INDEX) return (size_t)zz * sWH + (size_t)yy * sW + (size_t)xx;
-        const float f = add_rn(add_rn(mul_rn(mul_rn((float)zz, fW), fH), mul_rn((float)yy, fW)), (float)xx);
+struct VoxelIndex {
+    int W, H; size_t n;
+    PH_HD size_t at(int xx, int yy, int zz) const {
+        if (!FLOAT_INDEX) return (size_t)zz * ((size_t)W * (size_t)H) + (size_t)yy * (size_t)W + (size_t)xx;
+        const float f = add_rn(add_rn(mul_rn(mul_rn((float)zz, (float)W), (float)H), mul_rn((float)yy, (float)W)), (float)xx);
         const size_t i = (size_t)f;
         return i < n ? i : n - 1;
-    };
-#define PH_AT(xx, yy, zz) (K * (PH_LDG(&rho[idx(xx, yy, zz)]) * 1.0f))
+    }
+};
+template <class Indexer>
+PH_HD f4 field_voxel_at(const Indexer &I, const float *rho, int x, int y, int z, int W, int H, int D, float gx, float gy, float gz) {
+    const float K = 0.225e-3f;
+    const size_t sW = (size_t)W, sWH = (size_t)W * (size_t)H;
+#define PH_AT(xx, yy, zz) (K * (PH_LDG(&rho[I.at(xx, yy, zz)]) * 1.0f))
     float c = PH_AT(x, y, z);
     f4 o;
     if (x < 1) o.x = (float)((-3.0 / 2 * c + 2 * PH_AT(x + 1, y, z) - 1.0 / 2 * PH_AT(x + 2, y, z)) / gx);
@@ -182,6 +191,11 @@ PH_HD f4 field_voxel(const float *rho, int x, int y, int z, int W, int H, int D,
     // the n-1 channel is addressed with integers in the reference too (trace.h:1990)
     o.w = K * (PH_LDG(&rho[(size_t)z * sWH + (size_t)y * sW + (size_t)x]) * 1.0f);
     return o;
+}
+template <bool FLOAT_INDEX>
+PH_HD f4 field_voxel(const float *rho, int x, int y, int z, int W, int H, int D, float gx, float gy, float gz) {
+    VoxelIndex<FLOAT_INDEX> I; I.W = W; I.H = H; I.n = (size_t)W * (size_t)H * (size_t)D;
+    return field_voxel_at(I, rho, x, y, z, W, H, D, gx, gy, gz);
 }
 
 }  // namespace ph
