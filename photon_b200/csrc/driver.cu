@@ -1251,7 +1251,31 @@ int nccl_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
     for (int g = 0; g < n; g++) { cudaSetDevice(res[g].scene->device); if (cudaStreamSynchronize(res[g].scene->stream) != cudaSuccess) { cudaGetLastError(); return 2; } }
     return 0;
 }
-void nccl_prepare(int n) { std::lock_guard<std::mutex> lk(g_nccl.mu); g_nccl.ensure(n); }
+// Communicator set-up AND the first collective (which loads NCCL's kernels and connects its channels: another
+// ~0.5 s on top of ncclCommInitAll, profiles r4g) on a throw-away buffer, so that the reduce of the first call costs
+// what it costs in every later call.  Runs on its own thread beside the field builds.
+void nccl_prepare(int n) {
+    std::lock_guard<std::mutex> lk(g_nccl.mu);
+    const bool first = g_nccl.ncomms == 0;
+    if (!g_nccl.ensure(n) || !first) return;
+    std::vector<float *> buf((size_t)n, nullptr);
+    std::vector<cudaStream_t> st((size_t)n, nullptr);
+    bool ok = true;
+    for (int g = 0; g < n && ok; g++)
+        ok = cudaSetDevice(g) == cudaSuccess && cudaStreamCreateWithFlags(&st[g], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaMalloc(&buf[g], 256 * sizeof(float)) == cudaSuccess && cudaMemsetAsync(buf[g], 0, 256 * sizeof(float), st[g]) == cudaSuccess;
+    if (ok) {
+        g_nccl.GroupStart();
+        for (int g = 0; g < n; g++) { cudaSetDevice(g); g_nccl.Reduce(buf[g], buf[g], 256, ncclFloat, ncclSum, 0, g_nccl.comms[g], st[g]); }
+        g_nccl.GroupEnd();
+    }
+    for (int g = 0; g < n; g++) {
+        cudaSetDevice(g);
+        if (st[g]) { cudaStreamSynchronize(st[g]); cudaStreamDestroy(st[g]); }
+        if (buf[g]) cudaFree(buf[g]);
+    }
+    cudaGetLastError();
+}
 #else
 int nccl_reduce_images(std::vector<ShardResult> &, int, size_t) { return 1; }
 void nccl_prepare(int) {}
