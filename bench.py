@@ -338,6 +338,23 @@ def run_workloads(lib, args, c3_call, fp32_peak, which):
                     finally:
                         del os.environ["PHOTON_STEP_SCALE"]
                 lib.photon_b200_unregister_field(b"c5"); del keep, c
+            elif name == "c5_2048":
+                # Optional (not in "auto"): C5 at its stated depth -- 2048^3 voxels, 32 GiB of density + 128 GiB of field
+                # on one GPU, past the reference's 1024-plane cut (PHOTON_FULL_DEPTH) and past 32-bit voxel indices.
+                os.environ["PHOTON_FULL_DEPTH"] = "1"
+                try:
+                    keep = _c5_field(lib, n=2048, nz=2048)
+                    c = scenes.c5_stress("mem:c5", n=2048, nz=2048, write_field=False)
+                    sc = ResidentScene(c)
+                    del keep; torch.cuda.empty_cache()      # the field is built; the density is no longer read
+                    n, ms, steps, rays = _time_resident(sc, 10000, reps=2, warm=1)
+                    out[name] = _entry(lib, ms, steps, rays, fp32_peak, field_bytes=16 * 2048 ** 3,
+                                       workload="C5 at full depth: BOS through a 2048^3 blob (PHOTON_FULL_DEPTH=1, 64-bit voxel index), "
+                                                "three optical elements; 1e4 points x 1000 rays per launch")
+                    sc.close()
+                    lib.photon_b200_unregister_field(b"c5"); del c
+                finally:
+                    del os.environ["PHOTON_FULL_DEPTH"]
             elif name == "cubic":
                 os.environ["PHOTON_INTERPOLATION"] = "cubic"
                 try:
