@@ -221,6 +221,25 @@ double photon_b200_measure_fp32_tflops(int device);
 /* The same loop with Blackwell's packed FFMA2 (two FP32 FMAs per issued instruction). */
 double photon_b200_measure_fp32x2_tflops(int device);
 
+/* photon_scene_export_u16 for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  This entry point has no counterpart in the reference.
+ * The caller owns input and output -- image_dev: float32[n_pixels] on a GPU (rewritten in
+ * place with the noisy image when image_noise > 0, exactly as photon_scene_export_u16 does to the scene's image);
+ * out_dev: uint16[n_pixels] on the same GPU -- and the two scratch buffers of the export kernels (the image after
+ * gain, the running maximum) live in one static device array of
+ *     256 + 4 * PHOTON_B200_EXPORT_STATIC_MAX_PIXELS bytes (16 MiB + 256 B, a 2048 x 2048 sensor),
+ * which every GPU that loads the library holds until the process exits.  The call allocates and frees nothing, on
+ * the device or through any allocating runtime routine; it enqueues one 4-byte memset and the two kernels on
+ * `stream` (a cudaStream_t; NULL = the default stream) and returns without waiting: out_dev is valid once the
+ * stream has been synchronised.  n_pixels beyond the maximum is rejected (returns 1, photon_b200_last_error() says
+ * so).  All calls on one GPU share the array: calls that overlap on the GPU (different streams or threads without an
+ * ordering between them) race on it.  The first call on each device looks the array's address up
+ * (cudaGetSymbolAddress); make that call outside a stream capture.  Returns 0 on success. */
+#define PHOTON_B200_EXPORT_STATIC_MAX_PIXELS (2048 * 2048)
+int photon_b200_export_u16_static(float *image_dev, long long n_pixels, float pixel_gain, int pixel_bit_depth,
+                                  int intensity_rescaling, float image_noise, unsigned int seed,
+                                  unsigned short *out_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

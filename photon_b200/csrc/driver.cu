@@ -1511,3 +1511,85 @@ static double measure_fp32(int device, bool packed) {
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
     return best;
 }
+
+// ---------------------------------------------------------------------------------
+// photon_b200_export_u16_static: image export that allocates nothing (include/photon_b200.h).
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// photon_scene_export_u16 takes its two scratch buffers -- the float image after gain (the input of pass 2) and the
+// word the block maxima are folded into -- from the library's memory pool on every call.  Here they live in one
+// file-scope device array of fixed size: [0, 256) the maximum (cleared by every call), [256, 256 + 4 n) the
+// intermediate image (overwritten by every call, never cleared).  Every GPU that loads the library holds the
+// 16 MiB + 256 B until the process exits.  In host code `g_export_scratch` is a host-side stand-in for the symbol, not
+// a device address: the address the kernels get comes from cudaGetSymbolAddress, asked once per device with that
+// device current.  All calls on one device share the array: calls that overlap on the GPU (two streams, two
+// threads) race on it.
+// ---------------------------------------------------------------------------------
+#define PH_EXPORT_STATIC_MAX_PIXELS ((size_t)PHOTON_B200_EXPORT_STATIC_MAX_PIXELS)
+static __device__ __align__(256) unsigned char g_export_scratch[256 + PH_EXPORT_STATIC_MAX_PIXELS * sizeof(float)];
+
+namespace {
+constexpr int kMaxScratchDevices = 64;
+std::mutex g_export_scratch_mutex;
+unsigned char *g_export_scratch_ptr[kMaxScratchDevices] = {nullptr};
+
+// Device address of g_export_scratch on `device`, which must be the current device.
+unsigned char *export_scratch_on(int device) {
+    if (device < 0 || device >= kMaxScratchDevices) { g_error = "export_u16_static: device ordinal out of range"; return nullptr; }
+    std::lock_guard<std::mutex> lk(g_export_scratch_mutex);
+    if (!g_export_scratch_ptr[device]) {
+        unsigned char *p = nullptr;
+        if (!cuda_ok(cudaGetSymbolAddress((void **)&p, g_export_scratch), "cudaGetSymbolAddress(g_export_scratch)", __FILE__, __LINE__)) return nullptr;
+        g_export_scratch_ptr[device] = p;
+    }
+    return g_export_scratch_ptr[device];
+}
+// The device a pointer lives on, or -1 if it is not device (or managed) memory.
+int device_of(const void *p) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return -1; }
+    if (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged) return -1;
+    return at.device;
+}
+}  // namespace
+
+extern "C" int photon_b200_export_u16_static(float *image_dev, long long n_pixels, float pixel_gain, int pixel_bit_depth,
+                                             int intensity_rescaling, float image_noise, unsigned int seed,
+                                             unsigned short *out_dev, void *stream) {
+    g_error.clear();
+    if (!image_dev || !out_dev || n_pixels < 0 || pixel_bit_depth < 1 || pixel_bit_depth > 16) { g_error = "export_u16_static: bad arguments"; return 1; }
+    if ((unsigned long long)n_pixels > (unsigned long long)PH_EXPORT_STATIC_MAX_PIXELS) {
+        char buf[256];
+        snprintf(buf, sizeof buf, "export_u16_static: %lld pixels exceed the static scratch of %zu pixels (PHOTON_B200_EXPORT_STATIC_MAX_PIXELS); "
+                                  "use photon_scene_export_u16", n_pixels, PH_EXPORT_STATIC_MAX_PIXELS);
+        g_error = buf;
+        return 1;
+    }
+    if (n_pixels == 0) return 0;
+    const int dev = device_of(image_dev);
+    if (dev < 0 || device_of(out_dev) != dev) { g_error = "export_u16_static: image_dev and out_dev must be device memory of one GPU"; return 1; }
+    int prev = -1;
+    if (!cuda_ok(cudaGetDevice(&prev), "cudaGetDevice", __FILE__, __LINE__)) return 1;
+    if (prev != dev && !cuda_ok(cudaSetDevice(dev), "cudaSetDevice", __FILE__, __LINE__)) return 1;
+    bool ok = false;
+    if (unsigned char *scratch = export_scratch_on(dev)) {
+        cudaStream_t st = (cudaStream_t)stream;
+        unsigned int *dmax = reinterpret_cast<unsigned int *>(scratch);
+        float *tmp = reinterpret_cast<float *>(scratch + 256);
+        const size_t n = (size_t)n_pixels;
+        const float gain = (float)std::pow(10.0, (double)pixel_gain / 20.0);
+        const float levels = (float)((1 << pixel_bit_depth) - 1);
+        const float k = (float)((65536.0 - 1.0) / ((double)(1 << pixel_bit_depth) - 1.0));
+        const unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8);
+        // the array keeps the last call's contents: the maximum must start at zero; tmp[0, n) is fully rewritten
+        ok = cuda_ok(cudaMemsetAsync(dmax, 0, sizeof(unsigned int), st), "export_u16_static: clear", __FILE__, __LINE__);
+        if (ok) {
+            export_prepare_kernel<<<blocks, 256, 0, st>>>(image_dev, tmp, n, gain, image_noise * 100.0f, seed, intensity_rescaling, dmax);
+            export_u16_kernel<<<blocks, 256, 0, st>>>(tmp, out_dev, n, levels, k, intensity_rescaling, dmax);
+            ok = cuda_ok(cudaGetLastError(), "export_u16_static: kernels", __FILE__, __LINE__);
+        }
+    }
+    if (prev != dev) cudaSetDevice(prev);
+    return ok ? 0 : 1;
+}

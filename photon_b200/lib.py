@@ -88,6 +88,9 @@ def load_library(require_gpu=False):
         lib.photon_b200_measure_fp32_tflops.restype = C.c_double
         lib.photon_b200_measure_fp32x2_tflops.argtypes = [C.c_int]
         lib.photon_b200_measure_fp32x2_tflops.restype = C.c_double
+        lib.photon_b200_export_u16_static.argtypes = [C.c_void_p, C.c_longlong, C.c_float, C.c_int, C.c_int, C.c_float, C.c_uint,
+                                                      C.c_void_p, C.c_void_p]
+        lib.photon_b200_export_u16_static.restype = C.c_int
         _lib = lib
     if require_gpu and _lib.photon_b200_device_count() < 1:
         raise PhotonLibraryError("no CUDA device visible; photon_b200 has no CPU fallback")
