@@ -206,11 +206,19 @@ bool build_field(DeviceField &F, const char *path, int device, cudaStream_t st) 
         CK(cudaMemcpyAsync(d_rho, src, n * sizeof(float), cudaMemcpyDefault, st));
     }
     CK(cudaMemsetAsync(d_min, 0xff, sizeof(unsigned int), st));
-    int blocks = (int)std::min<size_t>((size_t)sy * sz, (size_t)148 * 16);      // rows (y, z); a multiple of the SM count when there are enough
-    // the reference's float-arithmetic voxel index (trace_core.cuh: field_voxel) differs from the integer one only
-    // above 2^24 voxels
+    // rows (y, z) in a grid-stride loop: exactly the CTAs that are resident at once (2368 = 2.67 waves of the 888 that fit
+    // left the last third of the kernel to a partial wave, ncu r4j)
     const char *gi = getenv("PHOTON_GRADIENT_INDEX");
     const bool float_index = n > ((size_t)1 << 24) && !(gi && strcmp(gi, "exact") == 0);
+    int per_sm = 0, sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if ((float_index ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, build_field_kernel<true>, 256, 0)
+                     : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, build_field_kernel<false>, 256, 0)) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError(); per_sm = 4;
+    }
+    int blocks = (int)std::min<size_t>((size_t)sy * sz, (size_t)sms * per_sm);
+    // (float_index: the reference's float-arithmetic voxel index (trace_core.cuh: field_voxel) differs from the integer one
+    // only above 2^24 voxels)
     if (float_index) build_field_kernel<true><<<blocks, 256, 0, st>>>(d_rho, F.lin, sx, sy, sz, (float)dx, (float)dy, (float)dz, d_min);
     else build_field_kernel<false><<<blocks, 256, 0, st>>>(d_rho, F.lin, sx, sy, sz, (float)dx, (float)dy, (float)dz, d_min);
     CK(cudaGetLastError());
