@@ -355,16 +355,22 @@ def run_workloads(lib, args, c3_call, fp32_peak, which):
                     lib.photon_b200_unregister_field(b"c5"); del c
                 finally:
                     del os.environ["PHOTON_FULL_DEPTH"]
-            elif name == "cubic":
+            elif name in ("cubic", "cubic_brick"):
                 os.environ["PHOTON_INTERPOLATION"] = "cubic"
+                if name == "cubic_brick":
+                    os.environ["PHOTON_CUBIC_BRICK"] = "1"       # the same loop on TMA-staged bricks (A/B, not in "auto")
                 try:
                     sc = ResidentScene(c3_call)
                     n, ms, steps, rays = _time_resident(sc, args.points_per_step, reps=2, warm=1)
                     out[name] = _entry(lib, ms, steps, rays, fp32_peak, flop_per_step=FLOP_PER_RAY_STEP_CUBIC,
-                                       workload=f"C3 with the tricubic B-spline sampler (PHOTON_INTERPOLATION=cubic), {args.grid}^3 coefficients")
+                                       workload=f"C3 with the tricubic B-spline sampler (PHOTON_INTERPOLATION=cubic), {args.grid}^3 coefficients"
+                                                + (", hot loop on TMA-staged bricks (PHOTON_CUBIC_BRICK=1)" if name == "cubic_brick" else ""))
+                    if name == "cubic_brick":
+                        out[name]["brick_timeouts"] = lib.photon_b200_brick_timeouts()
                     sc.close()
                 finally:
                     del os.environ["PHOTON_INTERPOLATION"]
+                    os.environ.pop("PHOTON_CUBIC_BRICK", None)
         except Exception as e:
             out[name] = {"error": repr(e)[:300]}
         drop()

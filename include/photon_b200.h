@@ -214,6 +214,11 @@ long long photon_b200_cache_bytes(void);           /* field bytes resident now, 
 /* Which trace kernel the calling thread's last launch ran: "<integrator>/<gatherer>/<dump|image|stats>[/fixed]",
  * e.g. "rk4/cells/image" (tests use it to prove which instantiation they compared). */
 const char *photon_b200_last_variant(void);
+/* PHOTON_CUBIC_BRICK=1 (with PHOTON_INTERPOLATION=cubic, coherent RK4 scenes) runs the cubic hot loop on bricks of the
+ * quad-row table staged per warp in shared memory by TMA (variant "rk4/cubic-brick/..."); same results bit for bit.
+ * This counter is the number of brick refills on the current device whose wait gave up and fell back to the table:
+ * 0 unless something is broken (tests assert it).  No counterpart in the reference. */
+int photon_b200_brick_timeouts(void);
 
 /* FP32 FMA throughput of the device in TFLOP/s, measured with a register-resident FFMA loop
  * (the roofline denominator for the trace kernel, which is FP32-issue bound, not HBM bound). */

@@ -6,6 +6,7 @@
 // the density field is built on the GPU and cached across calls, all source points go
 // through one persistent launch unless ray dumps force the reference's per-batch files,
 // every CUDA call is checked, and nothing ever calls exit() inside the host process.
+#include <cuda.h>              // CUtensorMap types only; cuTensorMapEncodeTiled is fetched through the runtime
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <math.h>
@@ -68,6 +69,7 @@ struct DeviceField {
     f4 *lin = nullptr;                   // [D][H][W] float4 (grad n, n-1)
     float *coef = nullptr;               // cubic mode: [D][H][W] B-spline coefficients of n-1 (built on demand)
     float4 *coefq = nullptr;             // ... and their quad rows (c[x..x+3] per voxel) for the cubic hot loop
+    void *coefq_tmap = nullptr;          // ... and a CUtensorMap of the quad rows in device memory (PHOTON_CUBIC_BRICK=1)
     float4 *cells = nullptr;             // coherent hot loop: [D][H][W][8] per-cell polynomial table (built on demand)
     bool cells_refused = false;          // it did not fit; do not try again for this field
     cudaArray_t arr = nullptr;           // optional 3-D array for the texture path
@@ -83,8 +85,9 @@ struct DeviceField {
         if (lin) cudaFree(lin);
         if (coef) cudaFree(coef);
         if (coefq) cudaFree(coefq);
+        if (coefq_tmap) cudaFree(coefq_tmap);
         if (cells) cudaFree(cells);
-        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; coefq = nullptr; cells = nullptr; cells_refused = false;
+        tex = 0; arr = nullptr; lin = nullptr; coef = nullptr; coefq = nullptr; coefq_tmap = nullptr; cells = nullptr; cells_refused = false;
     }
 };
 // The field cache.  An entry is keyed by (device, path, mtime, size) and REFERENCE COUNTED: every scene (and every
@@ -274,6 +277,35 @@ bool ensure_coefficients(DeviceField &F, cudaStream_t st) {
     return true;
 }
 
+// Tensor map of the quad-row table for the TMA-staged cubic hot loop (CubicGatherBrick): the table seen as
+// float[D][H][4 W], box = BXQ quad rows x BY x BZ, no swizzle, out-of-range rows filled with zeros (never read).
+// The descriptor lives in device memory (128 bytes) and is handed to the kernel as a pointer.
+bool ensure_brick_map(DeviceField &F, cudaStream_t st) {
+    if (F.coefq_tmap) return true;
+    if (!F.coefq) { g_error = "PHOTON_CUBIC_BRICK needs the quad-row table (it did not fit)"; return false; }
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess || !fn) {
+        cudaGetLastError(); g_error = "cuTensorMapEncodeTiled is not available from this driver"; return false;
+    }
+    alignas(64) CUtensorMap tm;
+    const cuuint64_t dims[3] = {(cuuint64_t)F.P.W * 4u, (cuuint64_t)F.P.H, (cuuint64_t)F.P.D};
+    const cuuint64_t strides[2] = {(cuuint64_t)F.P.W * 16u, (cuuint64_t)F.P.W * (cuuint64_t)F.P.H * 16u};   // bytes, dims 1 and 2
+    const cuuint32_t box[3] = {CubicBrickShape::BXQ * 4u, (cuuint32_t)CubicBrickShape::BY, (cuuint32_t)CubicBrickShape::BZ};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = reinterpret_cast<encode_fn>(fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, F.coefq, dims, strides, box, estr,
+                                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { g_error = "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")"; return false; }
+    CK(cudaMalloc(&F.coefq_tmap, sizeof tm));
+    CK(cudaMemcpyAsync(F.coefq_tmap, &tm, sizeof tm, cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    return true;
+}
+
 // The per-cell polynomial table costs 128 B per voxel (8x the texels: 16 GiB at 512^3).  It is built when it fits
 // in PHOTON_CELLS_MAX_GIB (default 40) and leaves a quarter of the free memory alone; otherwise the coherent loop
 // reads the texels (LinearFieldCoherent).  Returns true when F.cells is there.
@@ -424,6 +456,7 @@ struct photon_scene {
     DeviceField *field = nullptr;
     bool use_texture = false;
     bool use_cubic = false;              // PHOTON_INTERPOLATION=cubic
+    bool use_brick = false;              // ... with the hot loop on TMA-staged bricks (PHOTON_CUBIC_BRICK=1, coherent RK4 scenes)
     int npoints = 0, point_offset = 0;   // shard of the caller's source points
     int total_points = 0, source_point_number = 0;
     float *d_sx = nullptr, *d_sy = nullptr, *d_sz = nullptr; double *d_srad = nullptr; int *d_sdiam = nullptr;
@@ -536,7 +569,12 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         gat = "cubic";
         BSplineField S; S.c = s->field->coef; S.quad = reinterpret_cast<const f4 *>(s->field->coefq); S.W = a.field.W; S.H = a.field.H; S.D = a.field.D;
         S.inv_sp = mk3(1.0f / s->field->spacing.x, 1.0f / s->field->spacing.y, 1.0f / s->field->spacing.z);
-        if (stats) trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        BSplineFieldBrick SB; static_cast<BSplineField &>(SB) = S; SB.tmap = s->field->coefq_tmap;
+        const bool brick = s->use_brick && SB.tmap && !stats && a.algorithm == 2;
+        if (brick) gat = "cubic-brick";
+        if (brick && dump) trace_rays_kernel<true, 2, BSplineFieldBrick><<<grid, PH_BLOCK, 0, s->stream>>>(a, SB);
+        else if (brick) trace_rays_kernel<false, 2, BSplineFieldBrick><<<grid, PH_BLOCK, 0, s->stream>>>(a, SB);
+        else if (stats) trace_rays_kernel<false, 2, BSplineField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (dump) trace_rays_kernel<true, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else trace_rays_kernel<false, 2, BSplineField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
     } else if (s->use_texture) {
@@ -783,6 +821,10 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
         if (s->use_cubic) {
             if (s->use_texture) { g_error = "PHOTON_INTERPOLATION=cubic is not available with PHOTON_SAMPLER=texture"; return false; }
             if (!ensure_coefficients(*s->field, s->stream)) return false;
+            // experiment kept as an option: the hot loop of coherent RK4 scenes on TMA-staged bricks of the quad-row table
+            { const char *bk = getenv("PHOTON_CUBIC_BRICK");
+              s->use_brick = bk && atoi(bk) != 0 && s->coherent && algorithm == 2;
+              if (s->use_brick && !ensure_brick_map(*s->field, s->stream)) return false; }
             // the spline of a constant region reproduces it to rounding only: keep the "below the global
             // minimum" fallback (trace.h:1056) from firing on the last bit
             a.field.data_min = a.field.data_min - 1e-4f * fabsf(a.field.data_min);
@@ -1174,6 +1216,12 @@ long long photon_b200_cache_bytes(void) {
 }
 // Which trace kernel the last launch of this host thread ran, e.g. "rk4/cells/dump" (tests assert on it).
 const char *photon_b200_last_variant(void) { return g_variant.c_str(); }
+// brick refills of the TMA-staged cubic loop whose mbarrier wait gave up, on the current device (0 unless something is broken)
+int photon_b200_brick_timeouts(void) {
+    unsigned int v = 0;
+    if (cudaMemcpyFromSymbol(&v, ph_brick_timeouts, sizeof v) != cudaSuccess) { cudaGetLastError(); return -1; }
+    return (int)v;
+}
 
 }  // extern "C"
 

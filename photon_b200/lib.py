@@ -82,6 +82,8 @@ def load_library(require_gpu=False):
         lib.photon_b200_cache_bytes.restype = C.c_longlong
         lib.photon_b200_last_variant.argtypes = []
         lib.photon_b200_last_variant.restype = C.c_char_p
+        lib.photon_b200_brick_timeouts.argtypes = []
+        lib.photon_b200_brick_timeouts.restype = C.c_int
         lib.photon_b200_sample_field.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         lib.photon_b200_sample_field.restype = C.c_int
         lib.photon_b200_measure_fp32_tflops.argtypes = [C.c_int]

@@ -264,3 +264,33 @@ def test_cuda_matches_oracle_cubic(alg, cubic_env, cuda_lib, oracle_lib, tmp_pat
     m = util.compare(ref, got, 10.0)
     print("cubic alg", alg, m)
     util.assert_parity("bos_cubic", m)
+
+
+@pytest.mark.gpu
+def test_tma_brick_loop_is_bit_identical_to_the_table_loop(cubic_env, cuda_lib, oracle_lib, tmp_path):
+    """PHOTON_CUBIC_BRICK=1: the cubic hot loop on per-warp bricks of the quad-row table staged in shared memory by TMA
+    (CubicGatherBrick, ray_stages.cuh).  Same taps and the same contraction as the table loop, so per-ray dumps and the
+    non-dump image must be IDENTICAL, the variant name proves which instantiation ran, no refill may time out, and the
+    result sits within the north-star bounds of the oracle like the table loop's."""
+    c = scenes.c3_bos(str(tmp_path / "b.nrrd"), n=64, dots_per_side=10, points_per_dot=10, rays_per_point=70, algorithm=2)
+    for d in ("o", "t", "b"):
+        (tmp_path / d).mkdir()
+    ref = util.run_with_dumps(oracle_lib, c, str(tmp_path / "o"))
+    tab = util.run_with_dumps(cuda_lib, c, str(tmp_path / "t"))
+    assert cuda_lib.photon_b200_last_variant().decode() == "rk4/cubic/dump"
+    img_tab = np.array(c.run(cuda_lib), np.float64)
+    os.environ["PHOTON_CUBIC_BRICK"] = "1"
+    try:
+        t0 = cuda_lib.photon_b200_brick_timeouts()
+        got = util.run_with_dumps(cuda_lib, c, str(tmp_path / "b"))
+        assert cuda_lib.photon_b200_last_variant().decode() == "rk4/cubic-brick/dump"
+        img_got = np.array(c.run(cuda_lib), np.float64)
+        assert cuda_lib.photon_b200_last_variant().decode() == "rk4/cubic-brick/image"
+        assert cuda_lib.photon_b200_brick_timeouts() == t0 >= 0
+    finally:
+        os.environ.pop("PHOTON_CUBIC_BRICK")
+    for a, b in zip(tab[1:], got[1:]):                       # per-ray positions and directions: the same bits (NaN = NaN)
+        assert np.array_equal(np.asarray(a), np.asarray(b), equal_nan=True)
+    rel = np.linalg.norm(img_got - img_tab) / np.linalg.norm(img_tab)
+    assert rel <= 1e-6, rel                                                # float atomics: summation order only
+    util.assert_parity("bos_cubic", util.compare(ref, got, 10.0))

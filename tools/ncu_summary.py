@@ -5,8 +5,9 @@ usage: python tools/ncu_summary.py gpurun_out/<tag>_trace.ncu-rep <tag> [ray_ste
 import csv, io, json, subprocess, sys
 rep, tag = sys.argv[1], sys.argv[2]
 steps = float(sys.argv[3]) if len(sys.argv) > 3 else 5.11e9
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-rows = list(csv.reader(io.StringIO(raw)))
+# a report, or the CSV of its raw page exported on the GPU box (gpurun brings back at most 64 MiB: reports stay there)
+raw = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = [r for r in csv.reader(io.StringIO(raw)) if len(r) > 20]
 hdr, units, vals = rows[0], rows[1], rows[2]
 col = {h: i for i, h in enumerate(hdr)}
 
