@@ -599,7 +599,13 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         if (g == G_COHERENT && occ != 3 && occ != 5) g = G_FANOUT;
         gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : "fanout";
         if (wide) gat = "wide";
-        if (wide && dump) trace_rays_kernel<true, 2, LinearFieldWide><<<grid, PH_BLOCK, 0, s->stream>>>(a, SW);
+        // scenes without a field, plain image launch: the two-phase kernel (rays that pass the first aperture are queued
+        // in shared memory and walk the lens system in full warps); PHOTON_QUEUE=0 keeps the fused kernel
+        const char *qe = getenv("PHOTON_QUEUE");
+        const bool queue_off = qe && atoi(qe) == 0;
+        const bool queued = !a.simulate_gradients && !dump && !stats && !fixed && !queue_off && occ == 3;
+        if (queued) { gat = "queue"; trace_nofield_kernel<3><<<grid, PH_BLOCK, 0, s->stream>>>(a); }
+        else if (wide && dump) trace_rays_kernel<true, 2, LinearFieldWide><<<grid, PH_BLOCK, 0, s->stream>>>(a, SW);
         else if (wide) trace_rays_kernel<false, 3, LinearFieldWide><<<grid, PH_BLOCK, 0, s->stream>>>(a, SW);
         else if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
         else if (fixed && dump) trace_rays_kernel<true, 2, LinearField, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);

@@ -16,9 +16,18 @@ PH_HD f3 ray_sphere(f3 c, float R, f3 d, f3 p) {
     float disc = (float)((double)(beta * beta) - 4.0 * (double)alpha * (double)gamma);
     if (disc < 0.0f) return nan3();
     float sq = sqrtf(disc);
+#if defined(__CUDA_ARCH__)
+    // (float)((double)a / (2.0 * (double)alpha)) for floats a, alpha: 2 alpha is exact, and binary64 carries more than
+    // 2 x 24 + 2 bits, so rounding its quotient to float gives the correctly rounded float quotient -- the same bits
+    // from one float division instead of two double ones (74 of the 1840 warp instructions of a PIV ray, ncu r4o)
+    const float den = __fmul_rn(2.0f, alpha);
+    float t1 = __fdiv_rn(__fadd_rn(-beta, sq), den);
+    float t2 = __fdiv_rn(__fadd_rn(-beta, -sq), den);
+#else
     double den = 2.0 * (double)alpha;
     float t1 = (float)((double)(-beta + sq) / den);
     float t2 = (float)((double)(-beta - sq) / den);
+#endif
     float t = (R > 0) ? (t1 <= t2 ? t1 : t2) : (t1 >= t2 ? t1 : t2);
     return p + d * t;
 }
@@ -102,6 +111,40 @@ PH_HD void refract_element(const Element &el, Ray &ray) {
         pos = hit;
     }
     ray.dir = dir; ray.pos = pos;
+}
+
+// The FIRST aperture test a ray meets in the optical train, on its own: true when refract_element would cull the ray
+// at the entry of the first stage's element (prt.cu:478-489 thin lens, 560-575 front surface of a thick lens, 880-895
+// first plane of an aperture) -- the same expressions on the same operands, so the same decision.  About half of all
+// rays end here (the lens samples cover a disc of radius lens_pitch, twice the aperture's: prt.cu:123-124 with
+// ray_cone_pitch_ratio = 1), which is what the no-field kernel's compaction uses (trace_kernel.cuh).  A NaN hit is
+// not a cull here either: it propagates and the ray is dropped by the NaN test after the train.
+PH_HD bool first_aperture_culls(const OpticalTrain &ot, const Ray &ray) {
+    int e = -1;
+    for (int s = 0; s < ot.stages && e < 0; s++) e = ot.order[s];
+    if (e < 0) return false;
+    const Element &el = ot.e[e];
+    const f3 dir = ray.dir, pos = ray.pos;
+    const f4 pl = el.plane;
+    const f3 n = mk3(pl.x, pl.y, pl.z);
+    const double half_pitch = (double)el.pitch / 2.0;
+    f3 hit;
+    if (el.type == 't') {
+        float t = -(dot(n, pos) + pl.w) / dot(n, dir);
+        hit = pos + dir * t;
+    } else if (el.type == 'l') {
+        float nmag = sqrtf(pl.x * pl.x + pl.y * pl.y + pl.z * pl.z);
+        float ds = (float)(el.vertex / 2.0 - (double)el.r_front);
+        f3 cf = el.centre + n * ds / nmag;
+        hit = ray_sphere(cf, el.r_front, dir, pos);
+    } else {
+        float nmag = sqrtf(pl.x * pl.x + pl.y * pl.y + pl.z * pl.z);
+        float ds = (float)(-el.vertex / 2.0);
+        float dtmp = pl.w - ds * nmag;
+        float t = -(dot(n, pos) + dtmp) / dot(n, dir);
+        hit = pos + dir * t;
+    }
+    return (double)axis_distance(hit, el.centre, pl) > half_pitch;
 }
 
 // prt.cu:1274-1381 with the intended element-per-stage order (deviation B-3).

@@ -116,6 +116,7 @@ inline bool fill_scene_args(TraceArgs &a, std::vector<f2> &aim, float lens_pitch
     c.p1y = (float)((double)(-c.pitch * (float)(c.ny - 1)) / 2.0);
     a.implement_diffraction = cam->implement_diffraction ? 1 : 0;
     if (c.nx < 1 || c.ny < 1) { err = "sensor has no pixels"; return false; }
+    if ((long long)c.nx * (long long)c.ny >= (1ll << 31)) { err = "sensor has 2^31 pixels or more (pixel indices are 32-bit)"; return false; }
     // any diffraction diameter renders (the reference has no bound either, prt.cu:1466-1540): footprints of more than
     // 8 rows leave the register path for one pair of erf per pixel (ray_optics.cuh: erf_splat)
 

@@ -68,15 +68,20 @@ struct SensorSample {
 
 // The per-ray pipeline in three pieces: generation (+ the move into the volume frame), the march, everything
 // after it (back to the camera frame, lens system, sensor).
-PH_HD Ray ray_prologue(const TraceArgs &a, int p, int lr, NormalStream &ns) {
-    float x_lens, y_lens;
-    unsigned long long ray_index = (unsigned long long)(p + a.global_point_offset) * (unsigned long long)a.rpp + (unsigned long long)lr;
+// aim point of ray lr of source point p on the lens, and the ray's global index (the key of its random streams)
+PH_HD void ray_aim(const TraceArgs &a, int p, int lr, float &x_lens, float &y_lens, unsigned long long &ray_index) {
+    ray_index = (unsigned long long)(p + a.global_point_offset) * (unsigned long long)a.rpp + (unsigned long long)lr;
     if (a.rpp == 1) { x_lens = 0.0f; y_lens = 0.0f; }
     else if (a.philox) {
         uint32_t c[4] = {(uint32_t)ray_index, (uint32_t)(ray_index >> 32), 0u, 0u};
         philox4x32_10(c, a.seed, 0x50484f54u);
         lens_aim(a.cone_ratio, a.lens_pitch, u01_24(c[0]), u01_24(c[1]), x_lens, y_lens);
     } else { x_lens = PH_LDG(&a.aim[lr].x); y_lens = PH_LDG(&a.aim[lr].y); }
+}
+PH_HD Ray ray_prologue(const TraceArgs &a, int p, int lr, NormalStream &ns) {
+    float x_lens, y_lens;
+    unsigned long long ray_index;
+    ray_aim(a, p, lr, x_lens, y_lens, ray_index);
     ns.ray = ray_index; ns.ctr = 0; ns.seed = a.seed;
     Ray ray = generate_ray(a.image_distance, a.mie, PH_LDG(&a.sx[p]), PH_LDG(&a.sy[p]), PH_LDG(&a.sz[p]),
                            PH_LDG(&a.sradiance[p]), PH_LDG(&a.sdiam[p]), a.wavelength, a.inv_fnum2, x_lens, y_lens);

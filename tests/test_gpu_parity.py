@@ -3,6 +3,7 @@
 import numpy as np
 import pytest
 
+from photon_b200 import scenes
 from tests import util
 
 pytestmark = pytest.mark.gpu
@@ -187,3 +188,56 @@ def test_c4_shaped_scene_matches_oracle(cuda_lib, oracle_lib, tmp_path):
     nof = util.run_with_dumps(oracle_lib, call, str(tmp_path / "n"))
     both = np.isfinite(ref[1][:, 0]) & np.isfinite(nof[1][:, 0])
     assert np.abs(ref[1][both] - nof[1][both])[:, :2].max() > 1e-3
+
+
+NOFIELD_CASES = ["piv_mie_thick_bilinear", "piv_diffuse_thin_bilinear", "piv_apparent", "piv_mie_thick_diffraction",
+                 "bos_nogradient", "piv_chief_ray_only"]
+
+
+@pytest.mark.parametrize("name", NOFIELD_CASES)
+def test_queued_nofield_kernel_matches_fused_kernel_and_oracle(name, cases, cuda_lib, oracle_lib, monkeypatch):
+    """Scenes without a field run trace_nofield_kernel on the plain image launch: rays that pass the first aperture
+    are queued in shared memory and walk the lens system, the sensor and the splat in full warps.  Every ray goes
+    through the same functions as in the fused kernel (PHOTON_QUEUE=0), so the images may differ by float summation
+    order only, the same rays must reach the sensor, and the image must sit within the north-star bound of the
+    oracle's."""
+    from photon_b200.scene import ResidentScene
+    call, _ = cases[name]
+    assert not call.save_lightrays and not call.simulate_density_gradients
+    ref = call.run(oracle_lib)
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("PHOTON_QUEUE", mode)
+        sc = ResidentScene(call)
+        sc.trace()
+        out[mode] = (np.array(sc.download_image(), np.float64), sc.sensor_hits, cuda_lib.photon_b200_last_variant().decode())
+        sc.close()
+    (img_q, hits_q, var_q), (img_f, hits_f, var_f) = out["1"], out["0"]
+    assert var_q == "nofield/queue/image" and var_f == "nofield/none/image", (var_q, var_f)
+    assert hits_q == hits_f and hits_q > 0
+    d = _rel_l2(img_q, img_f)
+    print(name, "queued vs fused:", d, "hits", hits_q, "vs oracle:", _rel_l2(img_q, ref))
+    assert d <= 2e-6, (name, d)
+    assert _rel_l2(img_q, ref) <= util.TOL_IMG_L2
+
+
+def test_queued_nofield_kernel_ragged_counts_and_position_noise(cuda_lib, monkeypatch):
+    """Ray counts that fill the queue unevenly (rpp = 1, 255, 256, 257, 1000: partial chunks, drains of fewer than 256
+    rays, several drains per point) and the position-noise stream, which is keyed by the ray's own number: the queued
+    kernel must give every ray the draws the fused kernel gives it."""
+    from photon_b200.scene import ResidentScene
+    for rpp, noise in ((1, 0.0), (255, 0.0), (256, 0.0), (257, 0.3), (1000, 0.3)):
+        call = scenes.c1_piv(particles=64, rays_per_particle=rpp)
+        if noise:
+            call.add_pos_noise = True
+            call.pos_noise_std = noise
+        imgs = {}
+        for mode in ("1", "0"):
+            monkeypatch.setenv("PHOTON_QUEUE", mode)
+            sc = ResidentScene(call)
+            sc.trace()
+            imgs[mode] = (np.array(sc.download_image(), np.float64), sc.sensor_hits)
+            sc.close()
+        assert imgs["1"][1] == imgs["0"][1], (rpp, imgs["1"][1], imgs["0"][1])
+        if imgs["0"][1]:
+            assert _rel_l2(imgs["1"][0], imgs["0"][0]) <= 2e-6, rpp
