@@ -453,7 +453,7 @@ def run_workloads_sharded(lib, args, rank, world, local, fp32_peak):
 def run_in_call(lib, call, world):
     """The library's OWN multi-GPU path: rank 0 alone makes ONE start_ray_tracing call over the whole C3 job
     with PHOTON_GPUS = N -- the library splits the source points over the N devices of the box, builds the field on each,
-    and combines the partial images with one ncclReduce onto device 0.  Cold (nothing cached: field read + built on
+    and combines the partial images onto device 0 with its own kernel over NVLink peer memory (PHOTON_REDUCE=nccl: one ncclReduce).  Cold (nothing cached: field read + built on
     every device, communicator set-up) then warm (second image of a BOS pair), then the same call on one GPU."""
     rays = call.num_particles * call.lightray_number_per_particle
     lib.photon_b200_release_cache()
@@ -476,7 +476,7 @@ def run_in_call(lib, call, world):
     res["rays_per_s_warm"] = rays / res["warm_s"]
     i1 = one.astype(np.float64)
     res["image_rel_l2_vs_sharded"] = float(np.linalg.norm(img - i1) / np.linalg.norm(i1))
-    res["note"] = "one start_ray_tracing call with host buffers per figure; NRRD file in the page cache; cold includes ncclCommInitAll"
+    res["note"] = "one start_ray_tracing call with host buffers per figure; NRRD file in the page cache; cold = first multi-GPU call of the process (contexts, field read + builds on every device); images combined by the library's peer-memory kernel"
     return res
 
 

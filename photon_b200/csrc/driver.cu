@@ -1249,6 +1249,62 @@ bool write_f3_file(const std::string &dir, const char *prefix, int k, const floa
 
 struct ShardResult { bool ok = false; photon_scene *scene = nullptr; std::vector<float> image; std::vector<long long> fixed; double scale = 0; };
 
+// The library's OWN image reduce over NVLink peer memory -- the default route of a PHOTON_GPUS call.  The partial
+// images live in the per-device pools of this library; device 0 is granted access to the other pools
+// (cudaMemPoolSetAccess, once per pool) and ONE kernel on device 0 reads every peer image through NVLink / NVSwitch and
+// adds them in device order onto its own (float sum in a fixed order: the same image for the same shards, run after
+// run; deterministic mode: exact 64-bit integer sum).  8 x 4 MiB cross the switch in tens of microseconds, and nothing
+// has to be set up first: the NCCL communicators this replaces cost the first call of a process seconds
+// (ncclCommInitAll + the first collective, contending with context creation on the other devices: the cold 8-GPU call
+// of r4k waited 1 s for them after its last device had finished tracing).  PHOTON_REDUCE=nccl keeps that route,
+// PHOTON_REDUCE=host sums through the host.
+#define PH_MAX_PEERS 16
+struct PeerImages { const void *p[PH_MAX_PEERS]; int n; };
+template <class T>
+__global__ void __launch_bounds__(256) peer_sum_kernel(T *__restrict__ dst, const PeerImages src, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        T acc = dst[i];
+        for (int g = 0; g < src.n; g++) acc += static_cast<const T *>(src.p[g])[i];
+        dst[i] = acc;
+    }
+}
+std::mutex g_peer_mutex;
+std::vector<int> g_peer_granted;         // devices whose pool device 0 may read
+// 0 = reduced onto device 0, 1 = peer access not available (nothing was enqueued)
+int peer_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
+    if (n - 1 > PH_MAX_PEERS) return 1;
+    photon_scene *s0 = res[0].scene;
+    const bool fixed = s0->d_fixed != nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_peer_mutex);
+        for (int g = 1; g < n; g++) {
+            photon_scene *s = res[g].scene;
+            if (s->device == s0->device) continue;
+            bool granted = false;
+            for (int d : g_peer_granted) if (d == s->device) granted = true;
+            if (granted) continue;
+            int can = 0;
+            if (!s->pool || cudaDeviceCanAccessPeer(&can, s0->device, s->device) != cudaSuccess || !can) { cudaGetLastError(); return 1; }
+            cudaMemAccessDesc d; memset(&d, 0, sizeof d);
+            d.location.type = cudaMemLocationTypeDevice; d.location.id = s0->device; d.flags = cudaMemAccessFlagsProtReadWrite;
+            if (cudaMemPoolSetAccess(s->pool, &d, 1) != cudaSuccess) { cudaGetLastError(); return 1; }
+            g_peer_granted.push_back(s->device);
+        }
+    }
+    PeerImages src; src.n = n - 1;
+    for (int g = 1; g < n; g++) src.p[g - 1] = fixed ? (const void *)res[g].scene->d_fixed : (const void *)res[g].scene->d_image;
+    if (cudaSetDevice(s0->device) != cudaSuccess) { cudaGetLastError(); return 1; }
+    const int blocks = (int)std::min<size_t>((npix + 255) / 256, (size_t)148 * 8);
+    if (fixed) peer_sum_kernel<unsigned long long><<<blocks, 256, 0, s0->stream>>>(s0->d_fixed, src, npix);
+    else peer_sum_kernel<float><<<blocks, 256, 0, s0->stream>>>(s0->d_image, src, npix);
+    if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(s0->stream) != cudaSuccess) {
+        cudaGetLastError();
+        fprintf(stderr, "libparallel_ray_tracing(b200): peer reduce failed\n");
+        return 2;                                            // device 0's image may be partly summed: the caller gives up
+    }
+    return 0;
+}
+
 // NCCL for the one exchange step the path has: the partial sensor images of a PHOTON_GPUS call are combined
 // with ONE ncclReduce over NVLink onto device 0.  The library is bound at run time (dlopen of
 // libnccl.so.2: no link-time dependency; without it the images are summed on the host, which is only a
@@ -1269,7 +1325,12 @@ struct NcclApi {
         if (tried) return h != nullptr;
         tried = true;
         if (const char *e = getenv("PHOTON_NCCL")) if (atoi(e) == 0) return false;
-        for (const char *name : {"libnccl.so.2", "libnccl.so"}) { h = dlopen(name, RTLD_NOW | RTLD_LOCAL); if (h) break; }
+        // PHOTON_NCCL_LIB names the file (photon_b200/lib.py points it at the NCCL that PyTorch bundles, when there is one:
+        // two different builds of libnccl.so.2 cannot live in one process, and whichever is loaded first would break
+        // the other's user -- found on an 8-GPU box, where `import torch` failed after this library had loaded the
+        // system's NCCL)
+        if (const char *f = getenv("PHOTON_NCCL_LIB")) if (*f) h = dlopen(f, RTLD_NOW | RTLD_LOCAL);
+        for (const char *name : {"libnccl.so.2", "libnccl.so"}) { if (h) break; h = dlopen(name, RTLD_NOW | RTLD_LOCAL); }
         if (!h) return false;
         CommInitAll = (decltype(CommInitAll))dlsym(h, "ncclCommInitAll");
         GroupStart = (decltype(GroupStart))dlsym(h, "ncclGroupStart");
@@ -1446,8 +1507,11 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
     // GPU, private images, one sum at the end.  One host thread per device.
     std::vector<ShardResult> res((size_t)ngpus);
     std::vector<std::thread> th;
-    // communicator set-up (0.67 s on the first call of a process) runs beside the field builds, not after the trace
-    std::thread nccl_init([ngpus]() { nccl_prepare(ngpus); });
+    // how the partial images are combined: peer (default: this library's own kernel over NVLink peer memory), nccl, host
+    const char *rm = getenv("PHOTON_REDUCE");
+    const bool use_nccl = rm && strcmp(rm, "nccl") == 0, use_host = rm && strcmp(rm, "host") == 0;
+    // NCCL route only: communicator set-up (seconds on the first call of a process) runs beside the field builds
+    std::thread nccl_init([ngpus, use_nccl]() { if (use_nccl) nccl_prepare(ngpus); });
     for (int g = 0; g < ngpus; g++) {
         th.emplace_back([&, g]() {
             auto t0 = std::chrono::steady_clock::now();
@@ -1470,9 +1534,11 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
     auto destroy_all = [&]() { for (int g = 0; g < ngpus; g++) if (res[g].scene) photon_scene_destroy(res[g].scene); };
     if (!all_ok) { destroy_all(); return; }
     lap("trace (all GPUs)");
-    const int red = nccl_reduce_images(res, ngpus, npix);             // one reduce over NVLink, then one D2H
+    int red = 1;                                                      // one reduce over NVLink, then one D2H
+    if (use_nccl) red = nccl_reduce_images(res, ngpus, npix);
+    else if (!use_host) red = peer_reduce_images(res, ngpus, npix);
     if (red == 0) {
-        lap("nccl reduce");
+        lap(use_nccl ? "nccl reduce" : "peer reduce");
         photon_scene_download_image(res[0].scene, image_array);      // folds the fixed-point sum first, if any
         lap("image D2H");
         destroy_all();
@@ -1483,7 +1549,7 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
         destroy_all();
         return;
     }
-    // no NCCL on this machine: the same sum through the host
+    // no peer access / no NCCL on this machine (or PHOTON_REDUCE=host): the same sum through the host
     const bool fixed = photon_scene_deterministic(res[0].scene) != 0;
     for (int g = 0; g < ngpus && all_ok; g++) {
         if (fixed) { res[g].fixed.resize(npix); all_ok = photon_scene_download_image_fixed(res[g].scene, res[g].fixed.data(), &res[g].scale) == 0; }

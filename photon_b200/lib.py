@@ -17,6 +17,23 @@ def library_path():
     return os.environ.get("PHOTON_B200_LIB") or _build.LIB
 
 
+def _point_at_bundled_nccl():
+    """PHOTON_REDUCE=nccl makes the library dlopen NCCL.  A Python process that also imports torch must end up with ONE
+    libnccl.so.2: point the library at the file PyTorch bundles (the nvidia-nccl wheel), found without importing torch."""
+    if os.environ.get("PHOTON_NCCL_LIB"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            f = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(f):
+                os.environ["PHOTON_NCCL_LIB"] = f
+                return
+    except Exception:
+        pass
+
+
 def load_library(require_gpu=False):
     """dlopen libparallel_ray_tracing.so (prebuilt in-tree) and declare the extended ABI."""
     global _lib
@@ -26,6 +43,7 @@ def load_library(require_gpu=False):
             raise PhotonLibraryError(
                 f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                 "(nvcc, sm_100a).  photon_b200 has no CPU fallback.")
+        _point_at_bundled_nccl()
         lib = C.CDLL(path)
         bind_start_ray_tracing(lib)
         lib.photon_b200_abi_version.restype = C.c_int

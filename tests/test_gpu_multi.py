@@ -1,6 +1,7 @@
 """Several GPUs inside one start_ray_tracing call (PHOTON_GPUS): source points split into contiguous
-shards, field replicated, partial images combined with one ncclReduce onto device 0 (or through the host with
-PHOTON_NCCL=0).  Needs two devices; skipped on a one-GPU box."""
+shards, field replicated, partial images combined onto device 0 by the library's own kernel over NVLink peer memory
+(default), by one ncclReduce (PHOTON_REDUCE=nccl) or through the host (PHOTON_REDUCE=host).  Needs two devices; skipped
+on a one-GPU box."""
 import os
 
 import numpy as np
@@ -35,20 +36,34 @@ def setup(tmp_path_factory, cuda_lib):
     return call, cuda_lib, base
 
 
-@pytest.mark.parametrize("nccl", [1, 0])
-def test_split_call_matches_one_gpu(setup, nccl):
+REDUCE = ["peer", "nccl", "host"]
+
+
+@pytest.mark.parametrize("reduce", REDUCE)
+def test_split_call_matches_one_gpu(setup, reduce):
     call, lib, base = setup
     one = _run(call, lib, base, PHOTON_GPUS=1)
-    two = _run(call, lib, base, PHOTON_GPUS=2, PHOTON_NCCL=nccl)
+    two = _run(call, lib, base, PHOTON_GPUS=2, PHOTON_REDUCE=reduce)
     assert (one - base).sum() > 0
     rel = np.linalg.norm(one.astype(np.float64) - two) / np.linalg.norm(one.astype(np.float64) - base)
     assert rel < 1e-5, rel                       # float atomics: order of the additions only
 
 
-@pytest.mark.parametrize("nccl", [1, 0])
-def test_split_call_is_bit_exact_in_deterministic_mode(setup, nccl):
+@pytest.mark.parametrize("reduce", REDUCE)
+def test_split_call_is_bit_exact_in_deterministic_mode(setup, reduce):
     call, lib, base = setup
     zero = np.zeros_like(base)
     one = _run(call, lib, zero, PHOTON_GPUS=1, PHOTON_DETERMINISTIC=1)
-    two = _run(call, lib, zero, PHOTON_GPUS=2, PHOTON_DETERMINISTIC=1, PHOTON_NCCL=nccl)
+    two = _run(call, lib, zero, PHOTON_GPUS=2, PHOTON_DETERMINISTIC=1, PHOTON_REDUCE=reduce)
     np.testing.assert_array_equal(one, two)
+
+
+def test_peer_reduce_gives_the_same_image_run_after_run(setup):
+    """The peer-memory reduce adds the shard images in device order: with the shards fixed, two calls differ only by
+    the float atomics inside each shard -- and not at all in deterministic mode (covered above).  Here: the default
+    route is the peer kernel and it agrees with the NCCL route to summation order."""
+    call, lib, base = setup
+    a = _run(call, lib, base, PHOTON_GPUS=2)
+    b = _run(call, lib, base, PHOTON_GPUS=2, PHOTON_REDUCE="nccl")
+    rel = np.linalg.norm(a.astype(np.float64) - b) / np.linalg.norm(a.astype(np.float64) - base)
+    assert rel < 1e-5, rel
