@@ -65,7 +65,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity leg of the cpu_baseline section")
-    ap.add_argument("--workloads", default="auto", help="comma list of c1_piv,c4_1024,c5,cubic | none | auto (all at N = 1, sharded C4/C5 at N = 8)")
+    ap.add_argument("--workloads", default="auto", help="comma list of c1_piv,c4_1024,c5,cubic,cubic_brick,c5_2048 | none | auto (all at N = 1, sharded C4/C5 at N = 8); N > 1: c5_full = the whole 1e10-ray C5 job")
     ap.add_argument("--no-in-call", action="store_true", help="N > 1: skip the PHOTON_GPUS leg")
     ap.add_argument("--workdir", default=None)
     return ap.parse_args()
@@ -379,7 +379,7 @@ def run_workloads(lib, args, c3_call, fp32_peak, which):
     return out
 
 
-def run_workloads_sharded(lib, args, rank, world, local, fp32_peak):
+def run_workloads_sharded(lib, args, rank, world, local, fp32_peak, which="auto"):
     """N > 1: BASELINE configs 4 and 5 over all ranks.  C4 AT ITS STATED SIZE (1e6 particles x 1000 rays x 2 frames
     through the 1024^3 field, 4 MP): every rank makes the same field on its GPU and traces its shard of the particles;
     partial images are summed with one NCCL reduce per frame.  C5: a slice of the 1e7-point list (1e5 points x 1000
@@ -395,6 +395,39 @@ def run_workloads_sharded(lib, args, rank, world, local, fp32_peak):
         mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         return float(mx[0]), float(sm[1]), float(sm[2])
+    if "c5_full" in which.split(","):
+        # Optional (not in "auto"): BASELINE config 5 AS STATED -- all 1e7 source points x 1000 rays = 1e10 rays through the
+        # 2048 x 2048 x 1024 field (replicated per GPU), three optical elements, step = spacing; each rank traces 1e7 / N points
+        # in ONE launch.  About 22 s of kernel time on 8 B200.
+        try:
+            keep = _c5_field(lib)
+            c = scenes.c5_stress("mem:c5", n=2048, nz=1024, write_field=False, dots_per_side=316, points_per_dot=100)
+            total = len(c.x)
+            per_rank = (total + world - 1) // world
+            sub = c.subset(slice(rank * per_rank, min(total, (rank + 1) * per_rank)))
+            sc = ResidentScene(sub, device=local)
+            del keep; torch.cuda.empty_cache()
+            sc.reset_counters()
+            torch.cuda.synchronize(); dist.barrier()
+            t0 = time.perf_counter()
+            sc.trace(); ms = sc.last_trace_ms
+            img = torch.from_numpy(sc.download_image().reshape(-1)).cuda()
+            dist.reduce(img, dst=0)
+            torch.cuda.synchronize(); dist.barrier()
+            wall = time.perf_counter() - t0
+            m, st, ry = reduce_max_sum(ms, sc.ray_steps, sc.rays)
+            out["c5_full_step_1"] = {"value": st / (m * 1e-3), "unit": "ray-steps/s", "rays": ry, "rays_per_s": ry / (m * 1e-3), "kernel_seconds": m * 1e-3,
+                                     "wall_seconds_with_reduce": wall, "gpus": world, "kernel": lib.photon_b200_last_variant().decode(),
+                                     "roofline_frac_per_gpu": st * 330.0 / (m * 1e-3) / 1e12 / fp32_peak / world if fp32_peak else None,
+                                     "image_sum": float(img.double().sum()) if rank == 0 else None,
+                                     "workload": f"BASELINE config 5 as stated: {total} source points x 1000 rays, 2048 x 2048 x 1024 field replicated per GPU, "
+                                                 "three optical elements, step = spacing, one launch per GPU"}
+            sc.close()
+            lib.photon_b200_unregister_field(b"c5"); del c
+        except Exception as e:
+            out["c5_full_step_1"] = {"error": repr(e)[:300]}
+        lib.photon_b200_release_cache(); torch.cuda.empty_cache()
+        return out
     try:
         c = scenes.c4_piv("mem:c4", n=1024, particles=1000000, rays_per_particle=1000, device="cuda", lib=lib)
         torch.cuda.empty_cache()
@@ -631,7 +664,7 @@ def main():
         elif world == 8 or wl != "auto":
             scene.close(); scene = None
             lib.photon_b200_release_cache()
-            workloads = run_workloads_sharded(lib, args, rank, world, local, fp32_peak)
+            workloads = run_workloads_sharded(lib, args, rank, world, local, fp32_peak, wl)
     if world > 1 and not args.no_in_call:
         if scene is not None:
             scene.close(); scene = None
