@@ -26,6 +26,9 @@ struct HostAcc {
 }
 
 extern "C" long long g_hostcheck_steps = 0;
+// the no-field kernel's queue rests on first_aperture_culls (ray_optics.cuh): a ray it culls must never reach the sensor.
+// Counted here for every ray of a scene without a field: rays it culls, and culled rays that produced a sample anyway.
+extern "C" long long g_hostcheck_culled = 0, g_hostcheck_cull_violations = 0, g_hostcheck_uncull_dead_in_train = 0;
 
 extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scattering_data_t *sc, char *scattering_type_str,
                                   lightfield_source_t *src, int rpp, float beam_wavelength, float f_number, int ne,
@@ -117,6 +120,12 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance, scatte
                 bool save = dumps && gid < num_lightrays_save;
                 SensorSample s = cubic ? trace_one<true>(a, SC, p, lr, gid, save, steps)
                                        : trace_one<true>(a, S, p, lr, gid, save, steps);
+                if (!simulate_density_gradients && a.train.e[0].type != 'n') {
+                    NormalStream ns0; Ray r0 = ray_prologue(a, p, lr, ns0);
+                    const bool cull = first_aperture_culls(a.train, r0);
+                    if (cull) { g_hostcheck_culled++; if (s.valid) g_hostcheck_cull_violations++; }
+                    else { Ray r1 = r0; optical_train(a.train, r1); if (any_nan(r1.pos) || any_nan(r1.dir)) g_hostcheck_uncull_dead_in_train++; }
+                }
                 if (!s.valid) continue;
                 if (erf_model) {
                     ErfFootprint fp; erf_footprint(fp, s.d_x, s.d_y, s.radiance, s.c4, a.cam.diffraction_diameter, erf_frac);

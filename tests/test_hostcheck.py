@@ -70,3 +70,30 @@ def test_large_footprints_on_the_host(model, diam, hostcheck_lib, oracle_lib):
     got = c.run(hostcheck_lib)
     assert ref.sum() > 0
     assert float(np.linalg.norm(got.astype(np.float64) - ref) / np.linalg.norm(ref.astype(np.float64))) <= 1e-7
+
+
+@pytest.mark.parametrize("kind", ["thick", "thin", "three_elements"])
+def test_first_aperture_test_agrees_with_the_optical_train(kind, hostcheck_lib):
+    """trace_nofield_kernel (scenes without a field) queues only the rays that pass first_aperture_culls
+    (ray_optics.cuh), which restates the first cull of refract_element on its own.  On the host, over every ray of a
+    scene: a ray it culls never yields a sensor sample, it does cull about half of all rays (the lens samples cover
+    twice the aperture's radius), and for a thin lens -- whose aperture test is the ONLY way to die in the train -- no
+    ray it lets through dies there: the two decisions are the same decision."""
+    import ctypes as C
+    from photon_b200 import scenes
+    if kind == "thin":
+        call = scenes.c1_piv(particles=150, rays_per_particle=400, mie=False, lens_model="thin-lens")
+    else:
+        call = scenes.c1_piv(particles=150, rays_per_particle=400)
+        if kind == "three_elements":
+            scenes.three_element_system(call)
+    cnt = {n: C.c_longlong.in_dll(hostcheck_lib, "g_hostcheck_" + n) for n in ("culled", "cull_violations", "uncull_dead_in_train")}
+    for c in cnt.values():
+        c.value = 0
+    img = call.run(hostcheck_lib)
+    rays = call.num_particles * call.lightray_number_per_particle
+    assert img.sum() > 0
+    assert cnt["cull_violations"].value == 0
+    assert 0.3 * rays < cnt["culled"].value < 0.7 * rays, (cnt["culled"].value, rays)
+    if kind == "thin":
+        assert cnt["uncull_dead_in_train"].value == 0
