@@ -3,6 +3,7 @@
 # with wall times.
 tag=${1:-r4r}
 out=gpurun_out; mkdir -p $out
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 | tee $out/${tag}_pytest.log
 ( time python -c "import __graft_entry__ as g; g.smoke()" ) 2>&1 | tail -5 | tee $out/${tag}_smoke.log
 ( time python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err ) 2>&1 | tail -3 | tee $out/${tag}_bench_time.log
 tail -3 $out/${tag}_bench.err
