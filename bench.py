@@ -65,7 +65,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity leg of the cpu_baseline section")
-    ap.add_argument("--workloads", default="auto", help="comma list of c1_piv,c4_1024,c5,cubic,cubic_brick,c5_2048 | none | auto (all at N = 1, sharded C4/C5 at N = 8); N > 1: c5_full = the whole 1e10-ray C5 job")
+    ap.add_argument("--workloads", default="auto", help="comma list of c1_piv,c4_1024,c5,cubic,c3_euler,cubic_brick,c5_2048 | none | auto (all at N = 1, sharded C4/C5 at N = 8); N > 1: c5_full = the whole 1e10-ray C5 job")
     ap.add_argument("--no-in-call", action="store_true", help="N > 1: skip the PHOTON_GPUS leg")
     ap.add_argument("--workdir", default=None)
     return ap.parse_args()
@@ -355,6 +355,16 @@ def run_workloads(lib, args, c3_call, fp32_peak, which):
                     lib.photon_b200_unregister_field(b"c5"); del c
                 finally:
                     del os.environ["PHOTON_FULL_DEPTH"]
+            elif name == "c3_euler":
+                # C3's scene with the Euler integrator (algorithm 1: what the reference's shipped BOS sample runs); one sample
+                # per step, SURVEY 8(d): ~100 FLOP and 128 B of texels per ray-step
+                import copy
+                ce = copy.copy(c3_call); ce.ray_tracing_algorithm = 1
+                sc = ResidentScene(ce)
+                n, ms, steps, rays = _time_resident(sc, args.points_per_step, reps=2, warm=1)
+                out[name] = _entry(lib, ms, steps, rays, fp32_peak, flop_per_step=100.0,
+                                   workload=f"C3 with the Euler integrator, {args.grid}^3 field; bound by the L1 data stage (8 LDG.128 per step), not by FP32")
+                sc.close()
             elif name in ("cubic", "cubic_brick"):
                 os.environ["PHOTON_INTERPOLATION"] = "cubic"
                 if name == "cubic_brick":
@@ -657,7 +667,7 @@ def main():
     wl = args.workloads
     if wl != "none":
         if world == 1:
-            which = ["c1_piv", "c4_1024", "c5", "cubic"] if wl == "auto" else [w for w in wl.split(",") if w]
+            which = ["c1_piv", "c4_1024", "c5", "cubic", "c3_euler"] if wl == "auto" else [w for w in wl.split(",") if w]
             scene.close(); scene = None
             lib.photon_b200_release_cache()
             workloads = run_workloads(lib, args, call, fp32_peak, which)
