@@ -61,23 +61,33 @@ PH_HD bool refract(f3 &dir, f3 N, float eta) {
 }
 
 // prt.cu:383-1011
-PH_HD void refract_element(const Element &el, Ray &ray) {
+// entry_hit: where the ray meets the element's first surface, when the caller already has it (first_aperture_culls of the
+// no-field kernel computed it, and that the ray passes the aperture there); null = compute and test it here.
+PH_HD void refract_element(const Element &el, Ray &ray, const f3 *entry_hit = nullptr) {
     f3 dir = ray.dir, pos = ray.pos;
     f4 pl = el.plane;
     f3 n = mk3(pl.x, pl.y, pl.z);
     const double half_pitch = (double)el.pitch / 2.0;
     if (el.type == 't') {
-        float t = -(dot(n, pos) + pl.w) / dot(n, dir);
-        f3 hit = pos + dir * t;
-        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        f3 hit;
+        if (entry_hit) hit = *entry_hit;
+        else {
+            float t = -(dot(n, pos) + pl.w) / dot(n, dir);
+            hit = pos + dir * t;
+            if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        }
         pos = hit;
         dir = normalize(-(pos - el.centre) / el.focal + dir);            // prt.cu:494-496
     } else if (el.type == 'l') {
         float nmag = sqrtf(pl.x * pl.x + pl.y * pl.y + pl.z * pl.z);
         float ds = (float)(el.vertex / 2.0 - (double)el.r_front);        // prt.cu:551
         f3 cf = el.centre + n * ds / nmag;
-        f3 hit = ray_sphere(cf, el.r_front, dir, pos);
-        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        f3 hit;
+        if (entry_hit) hit = *entry_hit;
+        else {
+            hit = ray_sphere(cf, el.r_front, dir, pos);
+            if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        }
         f3 N = normalize(hit - cf);
         float eta = is_nan(el.abbe) ? (float)(1.0 / el.n_glass)
                                     : (float)(1.0 / dispersed_index(el.n_glass, el.abbe, ray.wavelength, true));
@@ -100,12 +110,15 @@ PH_HD void refract_element(const Element &el, Ray &ray) {
         float nmag = sqrtf(pl.x * pl.x + pl.y * pl.y + pl.z * pl.z);
         float ds = (float)(-el.vertex / 2.0);
         float dtmp = pl.w - ds * nmag;
-        float t = -(dot(n, pos) + dtmp) / dot(n, dir);
-        f3 hit = pos + dir * t;
-        if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        f3 hit;
+        if (!entry_hit) {
+            float t = -(dot(n, pos) + dtmp) / dot(n, dir);
+            hit = pos + dir * t;
+            if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
+        }
         ds = (float)(el.vertex / 2);
         dtmp = pl.w - ds * nmag;
-        t = -(dot(n, pos) + dtmp) / dot(n, dir);
+        float t = -(dot(n, pos) + dtmp) / dot(n, dir);
         hit = pos + dir * t;
         if ((double)axis_distance(hit, el.centre, pl) > half_pitch) { kill(ray); return; }
         pos = hit;
@@ -119,7 +132,7 @@ PH_HD void refract_element(const Element &el, Ray &ray) {
 // rays end here (the lens samples cover a disc of radius lens_pitch, twice the aperture's: prt.cu:123-124 with
 // ray_cone_pitch_ratio = 1), which is what the no-field kernel's compaction uses (trace_kernel.cuh).  A NaN hit is
 // not a cull here either: it propagates and the ray is dropped by the NaN test after the train.
-PH_HD bool first_aperture_culls(const OpticalTrain &ot, const Ray &ray) {
+PH_HD bool first_aperture_culls(const OpticalTrain &ot, const Ray &ray, f3 *hit_out = nullptr) {
     int e = -1;
     for (int s = 0; s < ot.stages && e < 0; s++) e = ot.order[s];
     if (e < 0) return false;
@@ -144,15 +157,17 @@ PH_HD bool first_aperture_culls(const OpticalTrain &ot, const Ray &ray) {
         float t = -(dot(n, pos) + dtmp) / dot(n, dir);
         hit = pos + dir * t;
     }
+    if (hit_out) *hit_out = hit;
     return (double)axis_distance(hit, el.centre, pl) > half_pitch;
 }
 
 // prt.cu:1274-1381 with the intended element-per-stage order (deviation B-3).
-PH_HD void optical_train(const OpticalTrain &ot, Ray &ray) {
+PH_HD void optical_train(const OpticalTrain &ot, Ray &ray, const f3 *entry_hit = nullptr) {
     for (int s = 0; s < ot.stages; s++) {
         int e = ot.order[s];
         if (e < 0) continue;
-        refract_element(ot.e[e], ray);
+        refract_element(ot.e[e], ray, entry_hit);
+        entry_hit = nullptr;                                             // only the first element the ray meets
         if (any_nan(ray.pos) || any_nan(ray.dir)) return;
     }
 }

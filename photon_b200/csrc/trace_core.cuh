@@ -95,7 +95,7 @@ PH_HD Ray ray_prologue(const TraceArgs &a, int p, int lr, NormalStream &ns) {
 }
 
 template <bool DUMP, bool STATS>
-PH_HD SensorSample ray_epilogue(const TraceArgs &a, Ray &ray, NormalStream &ns, long long gid, bool save) {
+PH_HD SensorSample ray_epilogue(const TraceArgs &a, Ray &ray, NormalStream &ns, long long gid, bool save, const f3 *entry_hit = nullptr) {
     SensorSample out; out.valid = false; out.d_x = out.d_y = 0; out.radiance = 0; out.c4 = 0; out.sflags = 0;
     if (a.simulate_gradients) {                                          // prt.cu:2100-2131
         f3 rp = mat_mul(a.cam.rot, ray.pos);
@@ -118,7 +118,7 @@ PH_HD SensorSample ray_epilogue(const TraceArgs &a, Ray &ray, NormalStream &ns, 
         hit.x = -hit.x * M; hit.y = -hit.y * M;
         ray.dir = dir;
     } else {
-        optical_train(a.train, ray);
+        optical_train(a.train, ray, entry_hit);
         if (any_nan(ray.dir) || any_nan(ray.pos)) return out;            // prt.cu:2172-2176
         hit = sensor_plane_hit(ray, a.cam);
         flip = a.implement_diffraction != 0;
