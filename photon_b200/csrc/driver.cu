@@ -473,6 +473,7 @@ struct photon_scene {
     int last_launches = 0, total_launches = 0;
     int grid_blocks = 0;
     int occupancy = 3;                   // resident CTAs per SM the trace kernel is compiled for (PHOTON_OCC)
+    bool occupancy_set = false;          // PHOTON_OCC was given (otherwise each gatherer runs its measured best)
     double *d_dots = nullptr;            // dot statistics [n_dots][8], see TraceArgs::dot_stats
     int *d_order = nullptr;              // processing order of the source points (Morton order of x, y), or null
     bool wide = false;                   // field of more than 2^32 voxels (or PHOTON_INDEX64=1): 64-bit voxel index in the hot loop
@@ -595,7 +596,7 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         enum { G_FANOUT, G_COHERENT, G_CELLS };
         const int occ = s->occupancy;
         int g = (stats || fixed || !a.simulate_gradients) ? G_FANOUT : s->use_cells ? G_CELLS : s->coherent ? G_COHERENT : G_FANOUT;
-        if (g == G_CELLS && occ != 3) g = G_COHERENT;
+        if (g == G_CELLS && occ != 3 && occ != 7) g = G_COHERENT;
         if (g == G_COHERENT && occ != 3 && occ != 5) g = G_FANOUT;
         gat = !a.simulate_gradients ? "none" : g == G_CELLS ? "cells" : g == G_COHERENT ? "coherent" : "fanout";
         if (wide) gat = "wide";
@@ -613,6 +614,10 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         else if (dump && g == G_CELLS) trace_rays_kernel<true, 2, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, SC);
         else if (dump && g == G_COHERENT) trace_rays_kernel<true, 2, LinearFieldCoherent><<<grid, PH_BLOCK, 0, s->stream>>>(a, SH);
         else if (dump) trace_rays_kernel<true, 2, LinearField><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
+        // the cell-table loop alone gains from more, smaller CTAs: 7 x 128 threads at 72 registers = 28 warps per SM against
+        // 3 x 256 at 80 = 24 (C3 1.162e11 -> 1.198e11; 6 x 128 at 80 registers 1.171e11, 8 x 128 at 64 registers 1.112e11:
+        // spills).  The corner-texel loops lose with it (C4 -23 %, C5 -8 %, Euler -11 %, profiles r5k-r5m) and keep 3 x 256.
+        else if (g == G_CELLS && (occ == 7 || !s->occupancy_set)) trace_rays_kernel<false, 7, LinearFieldCells, false, 128><<<grid, 128, 0, s->stream>>>(a, SC);
         else if (g == G_CELLS) trace_rays_kernel<false, 3, LinearFieldCells><<<grid, PH_BLOCK, 0, s->stream>>>(a, SC);
         else if (g == G_COHERENT && occ == 5) trace_rays_kernel<false, 5, LinearFieldCoherent, false, 128><<<grid, 128, 0, s->stream>>>(a, SH);
         else if (g == G_COHERENT) trace_rays_kernel<false, 3, LinearFieldCoherent><<<grid, PH_BLOCK, 0, s->stream>>>(a, SH);
@@ -870,7 +875,7 @@ static bool scene_fill(photon_scene *s, float lens_pitch, float image_distance,
     // persistent grid: a multiple of the SM count (148 on B200), 2 CTAs resident per SM
     int sm_count = 148;
     CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device));
-    if (const char *o = getenv("PHOTON_OCC")) s->occupancy = std::max(2, std::min(6, atoi(o)));
+    if (const char *o = getenv("PHOTON_OCC")) { s->occupancy = std::max(2, std::min(7, atoi(o))); s->occupancy_set = true; }
     // One source point per CTA up to 64 CTAs per SM-slot: the block scheduler balances the tail of a launch at the
     // granularity of one point (r1w: 12 CTAs per SM striding over the points lost 2.3 % to the last wave).
     int mult = 64;
