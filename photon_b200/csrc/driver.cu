@@ -1276,26 +1276,30 @@ __global__ void __launch_bounds__(256) peer_sum_kernel(T *__restrict__ dst, cons
 std::mutex g_peer_mutex;
 std::vector<int> g_peer_granted;         // devices whose pool device 0 may read
 // 0 = reduced onto device 0, 1 = peer access not available (nothing was enqueued)
+// Let device `reader` read the pool of scene s's device (once per pool).  Called by each device thread of a PHOTON_GPUS
+// call as soon as its scene exists -- the grants (tens of ms each in a fresh process: the driver sets up the peer
+// mapping) then run side by side behind the field builds instead of one after the other in front of the reduce (the cold
+// 8-GPU call of r6b spent 195 ms there) -- and again, as a check, by the reduce itself.
+bool grant_peer_access(photon_scene *s, int reader) {
+    if (s->device == reader) return true;
+    {
+        std::lock_guard<std::mutex> lk(g_peer_mutex);
+        for (int d : g_peer_granted) if (d == s->device) return true;
+    }
+    int can = 0;
+    if (!s->pool || cudaDeviceCanAccessPeer(&can, reader, s->device) != cudaSuccess || !can) { cudaGetLastError(); return false; }
+    cudaMemAccessDesc d; memset(&d, 0, sizeof d);
+    d.location.type = cudaMemLocationTypeDevice; d.location.id = reader; d.flags = cudaMemAccessFlagsProtReadWrite;
+    if (cudaMemPoolSetAccess(s->pool, &d, 1) != cudaSuccess) { cudaGetLastError(); return false; }
+    std::lock_guard<std::mutex> lk(g_peer_mutex);
+    g_peer_granted.push_back(s->device);
+    return true;
+}
 int peer_reduce_images(std::vector<ShardResult> &res, int n, size_t npix) {
     if (n - 1 > PH_MAX_PEERS) return 1;
     photon_scene *s0 = res[0].scene;
     const bool fixed = s0->d_fixed != nullptr;
-    {
-        std::lock_guard<std::mutex> lk(g_peer_mutex);
-        for (int g = 1; g < n; g++) {
-            photon_scene *s = res[g].scene;
-            if (s->device == s0->device) continue;
-            bool granted = false;
-            for (int d : g_peer_granted) if (d == s->device) granted = true;
-            if (granted) continue;
-            int can = 0;
-            if (!s->pool || cudaDeviceCanAccessPeer(&can, s0->device, s->device) != cudaSuccess || !can) { cudaGetLastError(); return 1; }
-            cudaMemAccessDesc d; memset(&d, 0, sizeof d);
-            d.location.type = cudaMemLocationTypeDevice; d.location.id = s0->device; d.flags = cudaMemAccessFlagsProtReadWrite;
-            if (cudaMemPoolSetAccess(s->pool, &d, 1) != cudaSuccess) { cudaGetLastError(); return 1; }
-            g_peer_granted.push_back(s->device);
-        }
-    }
+    for (int g = 1; g < n; g++) if (!grant_peer_access(res[g].scene, s0->device)) return 1;
     PeerImages src; src.n = n - 1;
     for (int g = 1; g < n; g++) src.p[g - 1] = fixed ? (const void *)res[g].scene->d_fixed : (const void *)res[g].scene->d_image;
     if (cudaSetDevice(s0->device) != cudaSuccess) { cudaGetLastError(); return 1; }
@@ -1524,6 +1528,7 @@ extern "C" void start_ray_tracing(float lens_pitch, float image_distance,
             if (!s) return;
             auto t1 = std::chrono::steady_clock::now();
             res[g].scene = s;
+            if (!use_nccl && !use_host) grant_peer_access(s, 0);              // early and best effort; the reduce checks again
             res[g].ok = (g != 0 || photon_scene_upload_image(s, image_array) == 0)     // accumulate onto the caller's image
                         && photon_scene_trace(s) == 0 && photon_scene_sync(s) == 0;
             if (timing) fprintf(stderr, "[photon timing] gpu %d: scene + field %8.3f ms, trace %8.3f ms (kernel %8.3f ms)\n", g,
