@@ -604,8 +604,12 @@ bool launch_trace(photon_scene *s, int point_begin, int point_count, int dump_ba
         // in shared memory and walk the lens system in full warps); PHOTON_QUEUE=0 keeps the fused kernel
         const char *qe = getenv("PHOTON_QUEUE");
         const bool queue_off = qe && atoi(qe) == 0;
-        const bool queued = !a.simulate_gradients && !dump && !stats && !fixed && !queue_off && occ == 3;
-        if (queued) { gat = "queue"; trace_nofield_kernel<3><<<grid, PH_BLOCK, 0, s->stream>>>(a); }
+        const bool queued = !a.simulate_gradients && !dump && !stats && !fixed && !queue_off && (occ == 3 || occ == 6);
+        // 6 CTAs per SM at 40 registers: the kernel is issue-bound on libm and IEEE division / square-root sequences, and
+        // 48 warps per SM hide more of their latency than the spills cost (C1 3.98 ms at 3 CTAs / 80 registers, 3.81 at 4,
+        // 3.67 at 5, 3.65 at 6, 3.69 at 8 / 32 registers: profiles r6e-r6g).  PHOTON_OCC=3 selects the 80-register build.
+        if (queued && occ == 3 && s->occupancy_set) { gat = "queue"; trace_nofield_kernel<3><<<grid, PH_BLOCK, 0, s->stream>>>(a); }
+        else if (queued) { gat = "queue"; trace_nofield_kernel<6><<<grid, PH_BLOCK, 0, s->stream>>>(a); }
         else if (wide && dump) trace_rays_kernel<true, 2, LinearFieldWide><<<grid, PH_BLOCK, 0, s->stream>>>(a, SW);
         else if (wide) trace_rays_kernel<false, 3, LinearFieldWide><<<grid, PH_BLOCK, 0, s->stream>>>(a, SW);
         else if (stats) trace_rays_kernel<false, 3, LinearField, false, PH_BLOCK, true><<<grid, PH_BLOCK, 0, s->stream>>>(a, S);
